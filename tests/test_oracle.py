@@ -1,0 +1,92 @@
+"""Pins the test-only CPU oracle (oracle/edt_oracle.c) before anything trusts it:
+  * the reference's single golden pair (README.md:8, image/sample_*.png) via tests/golden/sample_pair.npz
+  * vectors produced by the stock OpenMP build (tests/golden/ref_vectors.npz, made by make_golden.py)
+  * the live stock build (oracle/_ref) on seeded square inputs where it is exact (side <= 4096)
+  * a brute-force nearest-seed search on small masks, square and not
+  * the degenerate known answers of SURVEY.md section 8(c)
+"""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+FLAGS = {"default": (1, True, False), "l": (0, True, False), "n": (1, False, False), "a": (1, True, True),
+         "ln": (0, False, False), "aln": (0, False, True)}
+
+
+def test_golden_pair(oracle):
+    z = np.load(os.path.join(GOLDEN, "sample_pair.npz"))
+    assert hashlib.sha256(z["out"].tobytes()).hexdigest() == \
+        "947ec2e8d10e1a5ff04f22fcf3011389c0329045eac5654b627ea96b715fdb87"
+    out = oracle.sdf(z["ya"], 200, 200, stride=2, offset=int(z["offset"]), test_above=bool(z["test_above"]),
+                     spread=int(z["spread"]), asymmetric=bool(z["asymmetric"]))
+    assert np.array_equal(out, z["out"])
+    assert (out == 0).sum() == 331 and out.max() == 255
+
+
+def test_ref_vectors(oracle):
+    z = np.load(os.path.join(GOLDEN, "ref_vectors.npz"))
+    g = z["grad_ya"]
+    n = g.shape[0]
+    for name, (off, above, asym) in FLAGS.items():
+        for s in (7, 64):
+            out = oracle.sdf(g, n, n, stride=2, offset=off, test_above=above, spread=s, asymmetric=asym)
+            assert np.array_equal(out, z[f"grad_{name}_s{s}"]), (name, s)
+    out, sdf, din, dout = oracle.sdf(z["noise_img"], 64, 64, spread=16, fields=True)
+    assert np.array_equal(out, z["noise_out"])
+    assert np.array_equal(sdf.view(np.uint32), z["noise_sdf"].view(np.uint32))  # 0 ulp
+    assert np.array_equal(np.sqrt(din.astype(np.float32)).view(np.uint32), z["noise_din"].view(np.uint32))
+    assert np.array_equal(np.sqrt(dout.astype(np.float32)).view(np.uint32), z["noise_dout"].view(np.uint32))
+
+
+def test_bruteforce_small(oracle):
+    rng = np.random.default_rng(11)
+    shapes = [(1, 1), (1, 9), (9, 1), (2, 2), (13, 40), (40, 13), (33, 33)]
+    shapes += [(int(rng.integers(2, 48)),) * 2 for _ in range(60)]
+    for (h, w) in shapes:
+        for dens in (0.0, 0.03, 0.5, 0.97, 1.0):
+            m = (rng.random((h, w)) < dens).astype(np.uint8)
+            for sv in (0, 1):
+                assert np.array_equal(oracle.edt_d2(m, sv), oracle.edt_d2(m, sv, brute=True)), (h, w, dens, sv)
+
+
+@pytest.mark.parametrize("n,spread", [(256, 16), (1024, 64), (2048, 100)])
+def test_live_reference_square(oracle, ref, n, spread):
+    img = oracle.syn_discs(n)
+    for asym in (False, True):
+        assert np.array_equal(oracle.sdf(img, n, n, spread=spread, asymmetric=asym),
+                              ref.sdf_u8(img, n, n, spread=spread, asymmetric=asym))
+    noise = oracle.syn_noise(n)
+    o_out, o_sdf, o_din, o_dout = oracle.sdf(noise, n, n, spread=spread, fields=True)
+    r_out, r_sdf, r_din, r_dout = ref.sdf_fields(noise, n, n, spread=spread)
+    assert np.array_equal(o_out, r_out)
+    assert np.array_equal(o_sdf.view(np.uint32), r_sdf.view(np.uint32))
+    # squared field: stock pre-sqrt floats are exact integers for side <= 4096
+    f = np.where(noise > 127, np.float32(0), np.float32(np.inf)).astype(np.float32)
+    assert np.array_equal(ref.d2_field(f).astype(np.int64), o_din.astype(np.int64))
+    assert np.array_equal(oracle.dist_transform_2d_binary(f).view(np.uint32),
+                          ref.dist_transform_2d(f).view(np.uint32))
+
+
+def test_degenerates(oracle):
+    n = 64
+    for val, exp in ((255, {"l": 255, "ln": 0}), (0, {"l": 0, "ln": 255}), (127, {"l": 0, "ln": 0}),
+                     (128, {"l": 255, "ln": 0})):
+        ya = np.full((n, n, 2), 255, np.uint8)
+        ya[..., 0] = val
+        for name, want in exp.items():
+            off, above, asym = FLAGS[name]
+            out = oracle.sdf(ya, n, n, stride=2, offset=off, test_above=above, spread=8, asymmetric=asym)
+            assert (out == want).all(), (val, name)
+        assert (oracle.sdf(ya, n, n, stride=2, offset=1, spread=8) == 255).all()  # alpha=255 everywhere
+
+
+def test_synthetic_generators_are_deterministic(oracle):
+    a = oracle.syn_discs(512)
+    assert hashlib.sha256(a.tobytes()).hexdigest() == hashlib.sha256(oracle.syn_discs(512).tobytes()).hexdigest()
+    assert 0.2 < (a > 127).mean() < 0.9
+    b = oracle.syn_noise(256)
+    assert abs((b > 127).mean() - 1 / 64) < 0.01
