@@ -1,0 +1,295 @@
+// api.cu -- the C ABI of include/chaqsdf.h over the sm_100a kernels. No CPU compute path exists here:
+// every entry point either launches the CUDA kernels or fails with an error code.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <tuple>
+
+#include "../../include/chaqsdf.h"
+#include "envelope.cuh"
+#include "rowscan.cuh"
+
+using namespace chaq;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<unsigned long long> g_launches{0};
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CQ_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (expr);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return fail(CHAQSDF_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));          \
+    } while (0)
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct DevInfo {
+    int sms = 0;
+    int max_smem_optin = 0;
+};
+std::mutex g_mu;
+std::map<int, DevInfo> g_dev;
+std::map<std::tuple<int, size_t, int>, QuantTable*> g_tables;
+
+int device_info(DevInfo* out) {
+    int dev = 0;
+    CQ_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_dev.find(dev);
+    if (it == g_dev.end()) {
+        DevInfo d;
+        CQ_CUDA(cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev));
+        CQ_CUDA(cudaDeviceGetAttribute(&d.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        it = g_dev.emplace(dev, d).first;
+    }
+    *out = it->second;
+    return CHAQSDF_OK;
+}
+
+// per-(device, spread, asymmetric) quantisation thresholds, built on the host from the reference's float
+// formula (tables.h) and kept on the device for the life of the process.
+int get_table(size_t spread, int asymmetric, const QuantTable** out) {
+    int dev = 0;
+    CQ_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto key = std::make_tuple(dev, spread, asymmetric ? 1 : 0);
+    auto it = g_tables.find(key);
+    if (it == g_tables.end()) {
+        QuantTable h;
+        build_quant_table(spread, asymmetric, &h);
+        QuantTable* d = nullptr;
+        CQ_CUDA(cudaMalloc(&d, sizeof(QuantTable)));
+        CQ_CUDA(cudaMemcpy(d, &h, sizeof(QuantTable), cudaMemcpyHostToDevice));
+        it = g_tables.emplace(key, d).first;
+    }
+    *out = it->second;
+    return CHAQSDF_OK;
+}
+
+int check_dims(size_t w, size_t h, size_t spread) {
+    if (w == 0 || h == 0) return fail(CHAQSDF_ERR_ARG, "empty image");
+    if (w > CHAQSDF_MAX_DIM || h > CHAQSDF_MAX_DIM) return fail(CHAQSDF_ERR_ARG, "image side exceeds 32768");
+    if (spread == 0) return fail(CHAQSDF_ERR_ARG, "spread must be a positive integer");  // sdfgen.c:233-236
+    if (spread >= 32767 && (w > 32767 || h > 32767))
+        return fail(CHAQSDF_ERR_ARG, "spread >= 32767 on a 32768-pixel side is not representable");
+    return CHAQSDF_OK;
+}
+
+int cap_for(size_t spread) { return spread + 1 > 0x7fff ? 0x7fff : (int)(spread + 1); }
+
+// launch geometry of pass 2
+struct EnvPlan {
+    int cap, nw, band_rows, nbands;
+    bool wide, global_ring;
+    size_t smem_bytes, ring_bytes;
+    dim3 grid;
+};
+
+int plan_envelope(size_t w, size_t buf_rows, size_t out_rows, size_t n_img, int cap, EnvPlan* pl) {
+    DevInfo di;
+    if (int rc = device_info(&di)) return rc;
+    pl->cap = cap;
+    pl->nw = ring_words(cap, (int)buf_rows);
+    pl->wide = cap > 1023;
+    const int lag = cap - 1 < (int)buf_rows ? cap - 1 : (int)buf_rows;
+    const size_t colblocks = (w + kEnvThreads - 1) / kEnvThreads;
+    // aim for ~1536 resident threads per SM; keep the halo re-read (2*lag rows per band) under ~50 %
+    long long target_threads = (long long)di.sms * 1536;
+    long long nb = target_threads / (long long)(colblocks * kEnvThreads * n_img);
+    if (nb < 1) nb = 1;
+    long long band = ((long long)out_rows + nb - 1) / nb;
+    long long min_band = 4LL * lag;
+    if (const char* e = getenv("CHAQSDF_BAND_ROWS")) band = atoll(e), min_band = 1;
+    if (band < min_band) band = min_band;
+    if (band > (long long)out_rows) band = (long long)out_rows;
+    if (band < 1) band = 1;
+    pl->band_rows = (int)band;
+    pl->nbands = (int)(((long long)out_rows + band - 1) / band);
+    const size_t ring_smem = (size_t)2 * pl->nw * kEnvThreads * sizeof(uint32_t);
+    pl->global_ring = ring_smem > 96 * 1024;
+    pl->smem_bytes = 516 * sizeof(uint32_t) + (pl->global_ring ? 0 : ring_smem);
+    pl->grid = dim3((unsigned)colblocks, (unsigned)pl->nbands, (unsigned)n_img);
+    pl->ring_bytes = pl->global_ring
+                         ? (size_t)2 * pl->nw * colblocks * kEnvThreads * pl->nbands * n_img * sizeof(uint32_t)
+                         : 0;
+    if (n_img > 65535 || pl->nbands > 65535) return fail(CHAQSDF_ERR_ARG, "batch or band count exceeds grid limits");
+    return CHAQSDF_OK;
+}
+
+template <bool WIDE, bool GR, bool FIELDS>
+int launch_env_t(const EnvPlan& pl, const EnvParams& p, cudaStream_t st) {
+    auto k = envelope_kernel<WIDE, GR, FIELDS>;
+    if (pl.smem_bytes > 48 * 1024)
+        CQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+    k<<<pl.grid, kEnvThreads, pl.smem_bytes, st>>>(p);
+    CQ_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return CHAQSDF_OK;
+}
+
+int launch_env(const EnvPlan& pl, const EnvParams& p, bool fields, cudaStream_t st) {
+    const int sel = (pl.wide ? 4 : 0) | (pl.global_ring ? 2 : 0) | (fields ? 1 : 0);
+    switch (sel) {
+        case 0: return launch_env_t<false, false, false>(pl, p, st);
+        case 1: return launch_env_t<false, false, true>(pl, p, st);
+        case 2: return launch_env_t<false, true, false>(pl, p, st);
+        case 3: return launch_env_t<false, true, true>(pl, p, st);
+        case 4: return launch_env_t<true, false, false>(pl, p, st);
+        case 5: return launch_env_t<true, false, true>(pl, p, st);
+        case 6: return launch_env_t<true, true, false>(pl, p, st);
+        default: return launch_env_t<true, true, true>(pl, p, st);
+    }
+}
+
+int launch_rowscan(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above, int cap,
+                   uint16_t* d_inter, cudaStream_t st) {
+    RowScanParams rp;
+    rp.img = d_img; rp.inter = d_inter; rp.rows = (long long)rows; rp.w = (int)w;
+    rp.stride = (int)stride; rp.offset = (int)offset; rp.above = test_above ? 1 : 0; rp.cap = cap;
+    rp.nwords = (int)((w + 31) / 32);
+    const size_t smem = (size_t)kRowWarps * rp.nwords * sizeof(uint32_t);
+    const unsigned blocks = (unsigned)((rows + kRowWarps - 1) / kRowWarps);
+    rowscan_kernel<<<blocks, kRowWarps * 32, smem, st>>>(rp);
+    CQ_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return CHAQSDF_OK;
+}
+
+}  // namespace
+
+namespace chaq {
+int set_error(int code, const char* msg) { return fail(code, msg); }
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+}  // namespace chaq
+
+// ------------------------------------------------------------------------------------------------
+//                                          C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+int chaqsdf_version(void) { return 100; }
+const char* chaqsdf_last_error_string(void) { return g_err.c_str(); }
+unsigned long long chaqsdf_launch_count(void) { return g_launches.load(); }
+
+size_t chaqsdf_batched_workspace_bytes(size_t n, size_t w, size_t h, size_t spread) {
+    if (check_dims(w, h, spread) || n == 0) return 0;
+    EnvPlan pl;
+    if (plan_envelope(w, h, h, n, cap_for(spread), &pl)) return 0;
+    return align_up(n * w * h * sizeof(uint16_t), 256) + pl.ring_bytes;
+}
+size_t chaqsdf_workspace_bytes(size_t w, size_t h, size_t spread) {
+    return chaqsdf_batched_workspace_bytes(1, w, h, spread);
+}
+size_t chaqsdf_envelope_workspace_bytes(size_t w, size_t buf_rows, size_t spread) {
+    if (check_dims(w, buf_rows, spread)) return 0;
+    EnvPlan pl;
+    if (plan_envelope(w, buf_rows, buf_rows, 1, cap_for(spread), &pl)) return 0;
+    return pl.ring_bytes;
+}
+size_t chaqsdf_fields_workspace_bytes(size_t w, size_t h) {
+    if (check_dims(w, h, 1)) return 0;
+    EnvPlan pl;
+    if (plan_envelope(w, h, h, 1, 0x7fff, &pl)) return 0;
+    return align_up(w * h * sizeof(uint16_t), 256) + pl.ring_bytes;
+}
+
+int chaqsdf_rowscan_device(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
+                           size_t spread, uint16_t* d_inter, void* stream) {
+    if (!d_img || !d_inter) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (w == 0 || rows == 0) return fail(CHAQSDF_ERR_ARG, "empty image");
+    if (w > CHAQSDF_MAX_DIM) return fail(CHAQSDF_ERR_ARG, "image side exceeds 32768");
+    if (spread == 0) return fail(CHAQSDF_ERR_ARG, "spread must be a positive integer");
+    if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
+    return launch_rowscan(d_img, w, rows, stride, offset, test_above, cap_for(spread), d_inter, (cudaStream_t)stream);
+}
+
+int chaqsdf_envelope_device(const uint16_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
+                            size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
+                            void* stream) {
+    if (!d_inter || !d_out) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (int rc = check_dims(w, buf_rows, spread)) return rc;
+    if (out_begin >= out_end || out_end > buf_rows) return fail(CHAQSDF_ERR_ARG, "bad output row range");
+    EnvPlan pl;
+    if (int rc = plan_envelope(w, buf_rows, out_end - out_begin, 1, cap_for(spread), &pl)) return rc;
+    if (pl.ring_bytes > workspace_bytes || (pl.ring_bytes && !d_workspace))
+        return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+    const QuantTable* tab;
+    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
+    EnvParams p{};
+    p.inter = d_inter; p.w = (int)w; p.buf_rows = (int)buf_rows;
+    p.out_begin = (int)out_begin; p.out_end = (int)out_end; p.band_rows = pl.band_rows;
+    p.cap = pl.cap; p.nw = pl.nw; p.table = tab; p.out = d_out; p.gring = (uint32_t*)d_workspace;
+    return launch_env(pl, p, false, (cudaStream_t)stream);
+}
+
+int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t h, size_t stride, size_t offset,
+                              int test_above, size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace,
+                              size_t workspace_bytes, void* stream) {
+    if (!d_imgs || !d_out || !d_workspace) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (n == 0) return fail(CHAQSDF_ERR_ARG, "empty batch");
+    if (int rc = check_dims(w, h, spread)) return rc;
+    if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
+    const int cap = cap_for(spread);
+    EnvPlan pl;
+    if (int rc = plan_envelope(w, h, h, n, cap, &pl)) return rc;
+    const size_t inter_bytes = align_up(n * w * h * sizeof(uint16_t), 256);
+    if (workspace_bytes < inter_bytes + pl.ring_bytes) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+    const QuantTable* tab;
+    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
+    uint16_t* inter = (uint16_t*)d_workspace;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (int rc = launch_rowscan(d_imgs, w, n * h, stride, offset, test_above, cap, inter, st)) return rc;
+    EnvParams p{};
+    p.inter = inter; p.w = (int)w; p.buf_rows = (int)h; p.out_begin = 0; p.out_end = (int)h;
+    p.band_rows = pl.band_rows; p.cap = cap; p.nw = pl.nw; p.table = tab; p.out = d_out;
+    p.gring = (uint32_t*)((char*)d_workspace + inter_bytes);
+    return launch_env(pl, p, false, st);
+}
+
+int chaqsdf_u8_device(const uint8_t* d_img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
+                      size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
+                      void* stream) {
+    return chaqsdf_u8_batched_device(d_img, 1, w, h, stride, offset, test_above, spread, asymmetric, d_out,
+                                     d_workspace, workspace_bytes, stream);
+}
+
+int chaqsdf_fields_device(const uint8_t* d_img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
+                          size_t spread, int asymmetric, int32_t* d_d2_in, int32_t* d_d2_out, float* d_f_in,
+                          float* d_f_out, float* d_sdf, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
+                          void* stream) {
+    if (!d_img || !d_workspace) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (int rc = check_dims(w, h, spread)) return rc;
+    if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
+    if (w > 32767 || h > 32767) return fail(CHAQSDF_ERR_ARG, "exact fields need sides <= 32767");
+    const int cap = 0x7fff;  // nothing saturates: every line distance is < 32767
+    EnvPlan pl;
+    if (int rc = plan_envelope(w, h, h, 1, cap, &pl)) return rc;
+    const size_t inter_bytes = align_up(w * h * sizeof(uint16_t), 256);
+    if (workspace_bytes < inter_bytes + pl.ring_bytes) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+    const QuantTable* tab;
+    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
+    uint16_t* inter = (uint16_t*)d_workspace;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (int rc = launch_rowscan(d_img, w, h, stride, offset, test_above, cap, inter, st)) return rc;
+    EnvParams p{};
+    p.inter = inter; p.w = (int)w; p.buf_rows = (int)h; p.out_begin = 0; p.out_end = (int)h;
+    p.band_rows = pl.band_rows; p.cap = cap; p.nw = pl.nw; p.table = tab; p.out = d_out;
+    p.d2_in = d_d2_in; p.d2_out = d_d2_out; p.f_in = d_f_in; p.f_out = d_f_out; p.sdf = d_sdf;
+    p.gring = (uint32_t*)((char*)d_workspace + inter_bytes);
+    return launch_env(pl, p, true, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,245 @@
+"""ctypes mirror of include/chaqsdf.h. Names follow the reference: dist_transform_2d (openmp/df.h:6) and the
+sdfgen.c pipeline (openmp/sdfgen.c:261-300) as sdf_u8*. Device functions take torch CUDA tensors."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libchaqsdf_b200.so")
+_lib = None
+
+
+class ChaqSdfError(RuntimeError):
+    pass
+
+
+def build_library(force=False):
+    """nvcc -gencode arch=compute_100a,code=sm_100a (csrc/Makefile). Cross-compiles without a GPU."""
+    if force and os.path.exists(LIB_PATH):
+        os.remove(LIB_PATH)
+    r = subprocess.run(["make", "-C", os.path.join(HERE, "csrc"), "-s"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise ChaqSdfError("building libchaqsdf_b200.so failed:\n" + r.stdout + r.stderr)
+    return LIB_PATH
+
+
+SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "dist_transform_2d",
+           "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
+           "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
+           "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
+           "chaqsdf_fields_device"]
+
+
+def lib():
+    """Load libchaqsdf_b200.so. No fallback: a missing library is an error."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ChaqSdfError(f"{LIB_PATH} not built: run __graft_entry__.build() (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    sz, vp, i = C.c_size_t, C.c_void_p, C.c_int
+    L.chaqsdf_last_error_string.restype = C.c_char_p
+    L.chaqsdf_launch_count.restype = C.c_ulonglong
+    L.dist_transform_2d.argtypes = [vp, sz, sz]
+    L.dist_transform_2d.restype = None
+    L.chaqsdf_u8.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp]
+    L.chaqsdf_workspace_bytes.argtypes = [sz, sz, sz]
+    L.chaqsdf_workspace_bytes.restype = sz
+    L.chaqsdf_batched_workspace_bytes.argtypes = [sz, sz, sz, sz]
+    L.chaqsdf_batched_workspace_bytes.restype = sz
+    L.chaqsdf_envelope_workspace_bytes.argtypes = [sz, sz, sz]
+    L.chaqsdf_envelope_workspace_bytes.restype = sz
+    L.chaqsdf_fields_workspace_bytes.argtypes = [sz, sz]
+    L.chaqsdf_fields_workspace_bytes.restype = sz
+    L.chaqsdf_u8_device.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp, sz, vp]
+    L.chaqsdf_u8_batched_device.argtypes = [vp, sz, sz, sz, sz, sz, i, sz, i, vp, vp, sz, vp]
+    L.chaqsdf_rowscan_device.argtypes = [vp, sz, sz, sz, sz, i, sz, vp, vp]
+    L.chaqsdf_envelope_device.argtypes = [vp, sz, sz, sz, sz, sz, i, vp, vp, sz, vp]
+    L.chaqsdf_fields_device.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp, vp, vp, vp, vp, vp, sz, vp]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise ChaqSdfError(f"chaqsdf error {rc}: {lib().chaqsdf_last_error_string().decode()}")
+
+
+def launch_count():
+    return int(lib().chaqsdf_launch_count())
+
+
+def _stream_ptr(stream):
+    import torch
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+# ---------------------------------------------------------------- host-buffer entry points
+def dist_transform_2d(img):
+    """reference openmp/df.h:6: in place on a C-contiguous float32 numpy array [h, w] of {0, +inf}."""
+    assert img.dtype == np.float32 and img.flags.c_contiguous and img.ndim == 2
+    h, w = img.shape
+    L = lib()
+    L.dist_transform_2d(img.ctypes.data_as(C.c_void_p), w, h)
+    _check(L.chaqsdf_dt2d_last_status())
+    return img
+
+
+def sdf_u8(img, w, h, stride=1, offset=0, test_above=True, spread=64, asymmetric=False, out=None):
+    """reference openmp/sdfgen.c:261-300 on host buffers (numpy, or pinned torch CPU tensors)."""
+    if out is None:
+        out = np.empty((h, w), np.uint8)
+    ip = img.ctypes.data_as(C.c_void_p) if isinstance(img, np.ndarray) else _ptr(img)
+    op = out.ctypes.data_as(C.c_void_p) if isinstance(out, np.ndarray) else _ptr(out)
+    if isinstance(img, np.ndarray):
+        assert img.dtype == np.uint8 and img.flags.c_contiguous and img.size >= w * h * stride
+    _check(lib().chaqsdf_u8(ip, w, h, stride, offset, int(test_above), spread, int(asymmetric), op))
+    return out
+
+
+# ---------------------------------------------------------------- device entry points (torch tensors)
+def workspace_bytes(w, h, spread, n=1):
+    return int(lib().chaqsdf_batched_workspace_bytes(n, w, h, spread))
+
+
+def _workspace(nbytes, device):
+    import torch
+    return torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+
+
+def sdf_u8_device(d_img, w, h, stride=1, offset=0, test_above=True, spread=64, asymmetric=False, out=None,
+                  workspace=None, stream=None):
+    import torch
+    if out is None:
+        out = torch.empty((h, w), dtype=torch.uint8, device=d_img.device)
+    if workspace is None:
+        workspace = _workspace(workspace_bytes(w, h, spread), d_img.device)
+    _check(lib().chaqsdf_u8_device(_ptr(d_img), w, h, stride, offset, int(test_above), spread, int(asymmetric),
+                                   _ptr(out), _ptr(workspace), workspace.numel(), _stream_ptr(stream)))
+    return out
+
+
+def sdf_u8_batched_device(d_imgs, n, w, h, stride=1, offset=0, test_above=True, spread=16, asymmetric=False, out=None,
+                          workspace=None, stream=None):
+    import torch
+    if out is None:
+        out = torch.empty((n, h, w), dtype=torch.uint8, device=d_imgs.device)
+    if workspace is None:
+        workspace = _workspace(workspace_bytes(w, h, spread, n), d_imgs.device)
+    _check(lib().chaqsdf_u8_batched_device(_ptr(d_imgs), n, w, h, stride, offset, int(test_above), spread,
+                                           int(asymmetric), _ptr(out), _ptr(workspace), workspace.numel(),
+                                           _stream_ptr(stream)))
+    return out
+
+
+def rowscan_device(d_img, w, rows, spread, d_inter, stride=1, offset=0, test_above=True, stream=None):
+    _check(lib().chaqsdf_rowscan_device(_ptr(d_img), w, rows, stride, offset, int(test_above), spread, _ptr(d_inter),
+                                        _stream_ptr(stream)))
+    return d_inter
+
+
+def envelope_device(d_inter, w, buf_rows, out_begin, out_end, spread, asymmetric, d_out, workspace=None, stream=None):
+    nb = int(lib().chaqsdf_envelope_workspace_bytes(w, buf_rows, spread))
+    if workspace is None and nb:
+        workspace = _workspace(nb, d_inter.device)
+    _check(lib().chaqsdf_envelope_device(_ptr(d_inter), w, buf_rows, out_begin, out_end, spread, int(asymmetric),
+                                         _ptr(d_out), _ptr(workspace), workspace.numel() if workspace is not None else 0,
+                                         _stream_ptr(stream)))
+    return d_out
+
+
+def sdf_fields_device(d_img, w, h, stride=1, offset=0, test_above=True, spread=64, asymmetric=False, want=("d2_in", "d2_out", "f_in", "f_out", "sdf", "out"),
+                      stream=None):
+    """Exact unwindowed fields (see chaqsdf_fields_device). Returns a dict of torch tensors."""
+    import torch
+    dev = d_img.device
+    dt = {"d2_in": torch.int32, "d2_out": torch.int32, "f_in": torch.float32, "f_out": torch.float32,
+          "sdf": torch.float32, "out": torch.uint8}
+    res = {k: torch.empty((h, w), dtype=dt[k], device=dev) for k in want}
+    ws = _workspace(int(lib().chaqsdf_fields_workspace_bytes(w, h)), dev)
+    g = lambda k: _ptr(res.get(k))  # noqa: E731
+    _check(lib().chaqsdf_fields_device(_ptr(d_img), w, h, stride, offset, int(test_above), spread, int(asymmetric),
+                                       g("d2_in"), g("d2_out"), g("f_in"), g("f_out"), g("sdf"), g("out"), _ptr(ws),
+                                       ws.numel(), _stream_ptr(stream)))
+    return res
+
+
+# ---------------------------------------------------------------- row-band sharding (multi-GPU)
+def shard_rows(h, world, rank):
+    """Rows [r0, r1) of an h-row image owned by `rank` (contiguous bands, remainder to the first ranks)."""
+    base, rem = divmod(h, world)
+    r0 = rank * base + min(rank, rem)
+    return r0, r0 + base + (1 if rank < rem else 0)
+
+
+def halo_plan(h, world, rank, spread):
+    """Which rows of the 16-bit intermediate this rank receives from / sends to which peer so that its pass 2
+    sees `spread` rows of context (or the image edge) around its band. Rows are image rows.
+    Returns (r0, r1, halo_top, halo_bot, recvs, sends) with recvs/sends = [(peer, a, b)], rows [a, b)."""
+    r0, r1 = shard_rows(h, world, rank)
+    halo_top, halo_bot = min(spread, r0), min(spread, h - r1)
+    recvs, sends = [], []
+    for other in range(world):
+        if other == rank:
+            continue
+        o0, o1 = shard_rows(h, world, other)
+        for (a, b) in ((max(o0, r0 - halo_top), min(o1, r0)), (max(o0, r1), min(o1, r1 + halo_bot))):
+            if a < b:
+                recvs.append((other, a, b))
+        oh_top, oh_bot = min(spread, o0), min(spread, h - o1)
+        for (a, b) in ((max(r0, o0 - oh_top), min(r1, o0)), (max(r0, o1), min(r1, o1 + oh_bot))):
+            if a < b:
+                sends.append((other, a, b))
+    return r0, r1, halo_top, halo_bot, recvs, sends
+
+
+def exchange_halos(inter, h, world, rank, spread, group=None):
+    """inter: [halo_top + rows + halo_bot, w] tensor whose middle rows are filled; fills the halo rows from
+    the neighbouring ranks with batched point-to-point ops (NCCL on GPU tensors, gloo on CPU tensors)."""
+    import torch.distributed as dist
+    r0, r1, halo_top, halo_bot, recvs, sends = halo_plan(h, world, rank, spread)
+    base = r0 - halo_top
+    ops = [dist.P2POp(dist.irecv, inter[a - base:b - base], peer, group) for (peer, a, b) in recvs]
+    ops += [dist.P2POp(dist.isend, inter[a - base:b - base], peer, group) for (peer, a, b) in sends]
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return inter
+
+
+def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, group=None, state=None, stride=1, offset=0,
+                   test_above=True):
+    """One image of h rows sharded by row bands over `world` ranks (one process per GPU). d_band holds this
+    rank's rows. Pass 1 is local; pass 2 needs `spread` rows of the 16-bit intermediate from each neighbour
+    band, exchanged point to point (NCCL over NVLink); then pass 2 is local. Returns this rank's output rows.
+    `state` (a dict) caches buffers between calls."""
+    import torch
+    r0, r1, halo_top, halo_bot, _, _ = halo_plan(h, world, rank, spread)
+    rows = r1 - r0
+    buf_rows = halo_top + rows + halo_bot
+    dev = d_band.device
+    if state is None:
+        state = {}
+    key = (w, h, spread, rank, world)
+    if state.get("key") != key:
+        state.clear()
+        state["key"] = key
+        state["inter"] = torch.empty((buf_rows, w), dtype=torch.int16, device=dev)
+        state["out"] = torch.empty((rows, w), dtype=torch.uint8, device=dev)
+        nb = int(lib().chaqsdf_envelope_workspace_bytes(w, buf_rows, spread))
+        state["ws"] = _workspace(nb, dev) if nb else None
+    inter, out = state["inter"], state["out"]
+    rowscan_device(d_band, w, rows, spread, inter[halo_top:halo_top + rows], stride=stride, offset=offset,
+                   test_above=test_above)
+    if world > 1:
+        exchange_halos(inter, h, world, rank, spread, group)
+    envelope_device(inter, w, buf_rows, halo_top, halo_top + rows, spread, asymmetric, out, workspace=state["ws"])
+    return out

@@ -1,0 +1,104 @@
+/*
+ * chaqsdf.h -- C ABI of libchaqsdf_b200.so, the B200 (sm_100a) replacement for the hot path of
+ * chaquator/chaq-sdfgen's OpenMP program. Plain pointers and sizes only; no C++/torch types.
+ * Citations are relative to the reference tree.
+ *
+ * What each entry point replaces:
+ *   dist_transform_2d          openmp/df.h:6 (same symbol, same signature; host pointer, in place)
+ *   chaqsdf_u8                 openmp/sdfgen.c:261-300 (transform_img_to_bool :52-62, transform_bool_to_float
+ *                              :65-72, dist_transform_2d x2 in OpenMP sections :277-289, transform_float_sub
+ *                              :98-106, transform_float_to_byte :75-96) on host buffers
+ *   chaqsdf_u8_device          the same, device-resident, stream-ordered, no allocation
+ *   chaqsdf_u8_batched_device  the same for a batch of equal-sized images (glyph atlases) in one launch pair
+ *   chaqsdf_rowscan_device /   the two passes separately, on row bands, for multi-GPU sharding (the
+ *   chaqsdf_envelope_device    reference has no multi-device path)
+ *   chaqsdf_fields_device      exact (unwindowed) squared-distance fields + the float fields of
+ *                              sdfgen.c:281-294, for parity checks
+ *
+ * All functions returning int return 0 on success, non-zero on error (chaqsdf_last_error_string()).
+ * There is no CPU fallback: without a CUDA device every compute entry fails with CHAQSDF_ERR_CUDA.
+ */
+#ifndef CHAQSDF_H
+#define CHAQSDF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CHAQSDF_OK 0
+#define CHAQSDF_ERR_ARG 1       /* bad argument (zero spread, oversize image, null pointer ...)  */
+#define CHAQSDF_ERR_CUDA 2      /* CUDA runtime error or no device                                */
+#define CHAQSDF_ERR_WORKSPACE 3 /* caller workspace too small                                     */
+
+#define CHAQSDF_MAX_DIM 32768      /* 15-bit line distances in the 16-bit intermediate            */
+#define CHAQSDF_D2_INF 2147483647  /* "no pixel of that class anywhere" in int32 D2 outputs       */
+
+int chaqsdf_version(void);
+const char* chaqsdf_last_error_string(void);
+
+/* Number of kernels this library has launched in this process (all threads); for bench accounting. */
+unsigned long long chaqsdf_launch_count(void);
+
+/* ---- df.h:6 drop-in -------------------------------------------------------------------------------
+ * img: host, row-major float[w*h], in place. Input heights 0 (seed) or +INF (no seed), as the CLI passes
+ * (sdfgen.c:281,286); output sqrtf of the exact squared Euclidean distance to the nearest seed, +INF if
+ * there is none. Thread-safe (called from two OpenMP section threads at sdfgen.c:277-289). Like the
+ * original it has no return value; on error it leaves img untouched and records the error string.
+ * Works for non-square images (the original does not: df.c:47, df.c:92). */
+void dist_transform_2d(float* img, size_t w, size_t h);
+int chaqsdf_dt2d_last_status(void); /* status of the calling thread's last dist_transform_2d */
+
+/* ---- fused host-buffer path (sdfgen.c:261-300) ----------------------------------------------------
+ * img: host bytes, pixel i at img[i*stride + offset] (stb's (Y,A) buffer: stride 2, offset 1 = alpha,
+ * 0 = luminance; sdfgen.c:264). test_above: px > 127 else px < 127 (sdfgen.c:57-59). out: host u8[w*h]. */
+int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
+               size_t spread, int asymmetric, uint8_t* out);
+
+/* ---- device-resident path -------------------------------------------------------------------------
+ * d_img/d_out/d_workspace are device pointers on the current device; stream is a cudaStream_t (NULL =
+ * default stream). No allocation or synchronisation inside once the per-(device,spread,asymmetric)
+ * quantisation table exists (first call with a new pair builds and uploads it). */
+size_t chaqsdf_workspace_bytes(size_t w, size_t h, size_t spread);
+int chaqsdf_u8_device(const uint8_t* d_img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
+                      size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
+                      void* stream);
+
+/* n images of w*h pixels each, image k at d_imgs + k*w*h*stride, output k at d_out + k*w*h. Images are
+ * independent (the batch is treated as separate lines, never as one tall image). */
+size_t chaqsdf_batched_workspace_bytes(size_t n, size_t w, size_t h, size_t spread);
+int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t h, size_t stride, size_t offset,
+                              int test_above, size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace,
+                              size_t workspace_bytes, void* stream);
+
+/* ---- the two passes, for row-band sharding --------------------------------------------------------
+ * Pass 1 (rows are independent): threshold + per-row distance to the nearest opposite-class pixel,
+ * saturated at spread+1, one uint16 per pixel (bit 15 = class, bits 0..14 = distance).
+ *   d_img: `rows` rows of the image band; d_inter: uint16[rows*w]. */
+int chaqsdf_rowscan_device(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset,
+                           int test_above, size_t spread, uint16_t* d_inter, void* stream);
+/* Pass 2 (columns; needs `spread` rows of context above and below each output row, or the image edge):
+ *   d_inter: uint16[buf_rows*w], any contiguous run of image rows; output rows [out_begin, out_end) of
+ *   that buffer are written to d_out[(r-out_begin)*w + x]. Rows the buffer does not hold are treated as
+ *   absent, which is exact when the buffer reaches the image edge or >= spread rows beyond the outputs. */
+size_t chaqsdf_envelope_workspace_bytes(size_t w, size_t buf_rows, size_t spread);
+int chaqsdf_envelope_device(const uint16_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
+                            size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace,
+                            size_t workspace_bytes, void* stream);
+
+/* ---- exact fields, for parity ---------------------------------------------------------------------
+ * Unwindowed exact EDT. Any output may be NULL. d2_in/d2_out: int32 squared distance to the nearest
+ * inside/outside pixel (CHAQSDF_D2_INF if none). f_in/f_out: sqrtf of those (+INF if none) = the reference's
+ * img_float_inside/outside after sdfgen.c:282,287. sdf: the field after sdfgen.c:294. out: the bitmap. */
+size_t chaqsdf_fields_workspace_bytes(size_t w, size_t h);
+int chaqsdf_fields_device(const uint8_t* d_img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
+                          size_t spread, int asymmetric, int32_t* d_d2_in, int32_t* d_d2_out, float* d_f_in,
+                          float* d_f_out, float* d_sdf, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
+                          void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CHAQSDF_H */

@@ -1,0 +1,193 @@
+"""CPU-only checks of the host side: the C-ABI library loads and exports every symbol include/chaqsdf.h
+declares; the pass-2 algorithm (the same envelope_core.h / tables.h the kernels compile) emulated on the host
+matches the oracle; the row-band halo exchange works with world_size 2 and 3 over gloo."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+sys.path.insert(0, ROOT)
+import __graft_entry__ as ge  # noqa: E402
+
+
+@pytest.fixture(scope="session")
+def pkg():
+    ge.build()
+    return ge.load_package()
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    hdr = open(os.path.join(ROOT, "include", "chaqsdf.h")).read()
+    declared = set(re.findall(r"\b(chaqsdf_\w+|dist_transform_2d)\s*\(", hdr))
+    assert declared == set(pkg.SYMBOLS), declared ^ set(pkg.SYMBOLS)
+    L = pkg.lib()
+    for s in declared:
+        assert hasattr(L, s), s
+    assert L.chaqsdf_version() == 100
+
+
+def test_no_gpu_means_error_not_fallback(pkg):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    img = np.zeros((8, 8), np.uint8)
+    with pytest.raises(pkg.ChaqSdfError):
+        pkg.sdf_u8(img, 8, 8, spread=4)
+    f = np.zeros((8, 8), np.float32)
+    with pytest.raises(pkg.ChaqSdfError):
+        pkg.dist_transform_2d(f)
+
+
+def test_product_does_not_touch_the_oracle():
+    for dp, _, fs in os.walk(os.path.join(ROOT, "chaq-sdfgen_b200")):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".c")) or f == "Makefile":
+                txt = open(os.path.join(dp, f), errors="ignore").read()
+                # mentions in comments are fine; loading, importing, linking or including is not
+                assert not re.search(r"oracle/|liboracle|libchaqref|import\s+oracle|from\s+oracle|oracle\.py|-loracle", txt), \
+                    os.path.join(dp, f)
+
+
+@pytest.fixture(scope="session")
+def emul(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("emul") / "libemul.so")
+    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-o", so,
+                    os.path.join(ROOT, "tests", "emul", "emul.cpp")], check=True)
+    L = C.CDLL(so)
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
+    i32p = np.ctypeslib.ndpointer(np.int32, flags="C")
+    L.emul_column_pass.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, i32p, u8p, C.c_void_p]
+    L.emul_quantise.argtypes = [i32p, u8p, C.c_size_t, C.c_size_t, C.c_int, u8p]
+    L.emul_ref_byte.argtypes = [C.c_int, C.c_longlong, C.c_size_t, C.c_int]
+    L.emul_ref_byte.restype = C.c_uint8
+    return L
+
+
+def _emul_u8(L, mask, spread, asym, band, wide=0, cap=None):
+    h, w = mask.shape
+    d2 = np.empty((h, w), np.int32)
+    cls = np.empty((h, w), np.uint8)
+    L.emul_column_pass(np.ascontiguousarray(mask), w, h, spread + 1 if cap is None else cap, band, wide, d2, cls, None)
+    out = np.empty((h, w), np.uint8)
+    L.emul_quantise(d2, cls, h * w, spread, int(asym), out)
+    return out, d2, cls
+
+
+def test_emulated_column_pass_matches_oracle(emul, oracle):
+    rng = np.random.default_rng(5)
+    for it in range(120):
+        h, w = int(rng.integers(1, 70)), int(rng.integers(1, 40))
+        dens = rng.choice([0.0, 0.01, 0.05, 0.3, 0.5, 0.9, 1.0])
+        mask = (rng.random((h, w)) < dens).astype(np.uint8)
+        if it % 3 == 0:
+            yy, xx = np.mgrid[0:h, 0:w]
+            mask = np.zeros((h, w), np.uint8)
+            for _ in range(3):
+                cy, cx, r = rng.integers(0, h), rng.integers(0, w), rng.integers(1, 12)
+                mask |= ((yy - cy) ** 2 + (xx - cx) ** 2 <= r * r).astype(np.uint8)
+        img = (mask * 255).astype(np.uint8)
+        for spread in (1, 2, 5, 16, 100):
+            for band in (0, 7, 33):
+                want = oracle.sdf(img, w, h, spread=spread, asymmetric=bool(it & 1))
+                got, _, cls = _emul_u8(emul, mask, spread, bool(it & 1), band)
+                assert np.array_equal(got, want) and np.array_equal(cls, mask), (it, h, w, spread, band)
+        # unwindowed: exact squared distance to the other class
+        _, d2, _ = _emul_u8(emul, mask, 4, False, 13, wide=1, cap=1 << 20)
+        opp = np.where(mask == 1, oracle.edt_d2(mask, 0), oracle.edt_d2(mask, 1))
+        assert np.array_equal(d2, opp)
+
+
+def test_emulated_discs_and_noise(emul, oracle):
+    img = oracle.syn_discs(384)
+    mask = (img > 127).astype(np.uint8)
+    for spread, band in ((16, 0), (64, 100), (300, 0)):
+        got, _, _ = _emul_u8(emul, mask, spread, False, band)
+        assert np.array_equal(got, oracle.sdf(img, 384, 384, spread=spread))
+    noise = oracle.syn_noise(200)
+    got, _, _ = _emul_u8(emul, (noise > 127).astype(np.uint8), 8, True, 50)
+    assert np.array_equal(got, oracle.sdf(noise, 200, 200, spread=8, asymmetric=True))
+
+
+def test_emulated_structured_shapes(emul, oracle):
+    """Shapes much larger than the spread: exercises the window ("forgetting") logic of envelope_core.h."""
+    rng = np.random.default_rng(2)
+    for it in range(80):
+        h, w = int(rng.integers(20, 260)), int(rng.integers(8, 120))
+        yy, xx = np.mgrid[0:h, 0:w]
+        mask = np.zeros((h, w), np.uint8)
+        for _ in range(int(rng.integers(1, 8))):
+            cy, cx, r = rng.integers(-20, h + 20), rng.integers(-20, w + 20), rng.integers(1, 90)
+            kind = it % 4
+            if kind == 0:
+                m = (yy - cy) ** 2 + (xx - cx) ** 2 <= r * r
+            elif kind == 1:
+                m = abs(yy - cy) + abs(xx - cx) <= r
+            elif kind == 2:
+                m = abs((yy - cy) * int(rng.integers(1, 4)) - (xx - cx) * int(rng.integers(1, 4))) <= r // 3
+            else:
+                m = (yy - cy) ** 2 * int(rng.integers(1, 5)) + (xx - cx) ** 2 <= r * r
+            mask = (mask & ~m.astype(np.uint8)) if rng.random() < 0.3 else (mask | m.astype(np.uint8))
+        img = (mask * 255).astype(np.uint8)
+        for spread in (int(rng.integers(1, 6)), int(rng.integers(6, 20)), int(rng.integers(20, 70))):
+            for band in (0, int(rng.integers(1, 80))):
+                got, _, _ = _emul_u8(emul, mask, spread, False, band)
+                assert np.array_equal(got, oracle.sdf(img, w, h, spread=spread)), (it, h, w, spread, band)
+
+
+def test_quantiser_thresholds_equal_float_formula(emul, oracle):
+    # every integer D2 up to beyond the cap, both classes, several spreads: table look-up == float pipeline
+    for spread, asym in ((1, 0), (7, 0), (64, 0), (64, 1), (100, 1), (256, 0), (1024, 0)):
+        top = (spread + 3) ** 2
+        step = 1 if top < 200000 else 7
+        d2 = np.arange(0, top, step, dtype=np.int32)
+        d2 = np.concatenate([d2, np.array([2**31 - 1], np.int32)])
+        for cls in (0, 1):
+            c = np.full(d2.shape, cls, np.uint8)
+            out = np.empty(d2.shape, np.uint8)
+            emul.emul_quantise(d2, c, d2.size, spread, asym, out)
+            want = np.array([emul.emul_ref_byte(cls, int(v), spread, asym) for v in d2[:-1]], np.uint8)
+            assert np.array_equal(out[:-1], want), (spread, asym, cls)
+            assert out[-1] == want[-1]  # "nothing in reach" saturates like the cap
+            # and the formula itself is the oracle's (sdfgen.c:98-106, :75-96)
+            for v in (1, 2, spread * spread, spread * spread + 1):
+                sd = oracle.L.oracle_signed_from_d2(v, 0) if cls else oracle.L.oracle_signed_from_d2(0, v)
+                assert oracle.L.oracle_byte_from_signed(sd, spread, asym) == emul.emul_ref_byte(cls, v, spread, asym)
+
+
+GLOO_WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+import __graft_entry__ as ge
+pkg = ge.load_package()
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", rank=rank, world_size=world)
+for (h, w, spread) in ((64, 5, 7), (10, 3, 4), (37, 8, 100)):
+    r0, r1, ht, hb, recvs, sends = pkg.halo_plan(h, world, rank, spread)
+    buf = torch.full((ht + (r1 - r0) + hb, w), -1, dtype=torch.int16)
+    buf[ht:ht + r1 - r0] = torch.arange(r0, r1, dtype=torch.int16)[:, None]
+    pkg.exchange_halos(buf, h, world, rank, spread)
+    want = torch.arange(r0 - ht, r1 + hb, dtype=torch.int16)[:, None].expand(-1, w)
+    assert torch.equal(buf, want), (rank, h, spread, buf[:, 0].tolist())
+    assert ht == min(spread, r0) and hb == min(spread, h - r1)
+dist.barrier()
+dist.destroy_process_group()
+print("ok", rank)
+'''
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_halo_exchange_gloo(tmp_path, world):
+    script = tmp_path / "worker.py"
+    script.write_text(GLOO_WORKER)
+    port = 29500 + world + (os.getpid() % 500)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), ROOT],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert r.stdout.count("ok") == world
