@@ -145,6 +145,10 @@ struct ColumnEnvelope {
         if (g >= cap) return;
         int popfloor = kBig;
         int lowb = cq_max(run0, t - 2 * lag);
+        // sites older than 2*lag rows are out of the ring and out of reach of every row still to be
+        // finished: forget them (they can neither be popped nor serve as the predecessor in a test)
+        if (top_p < lowb) { top_p = -1; sec_p = -1; }
+        else if (sec_p < lowb) sec_p = -1;
         while (top_p >= 0 && sec_p >= 0 && dominated(sec_p, sec_g, top_p, top_g, t, g)) {
             int i = ridx(top_p >> 5);
             c.hull_set(i, c.hull_get(i) & ~(1u << (top_p & 31)));

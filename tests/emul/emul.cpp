@@ -30,11 +30,13 @@ struct Ctx {
     std::vector<uint32_t> hull, chg;
     int* d2; uint8_t* cls; int row0;
     long nld = 0;
-    uint32_t ld(int r) { ++nld; return col[(size_t)r * stride]; }
-    uint32_t hull_get(int i) { return hull[i]; }
-    void hull_set(int i, uint32_t v) { hull[i] = v; }
-    uint32_t chg_get(int i) { return chg[i]; }
-    void chg_set(int i, uint32_t v) { chg[i] = v; }
+    uint32_t ld(int r) { ++nld; if (r < 0 || r >= nrows) { ++oob; return 0; } return col[(size_t)r * stride]; }
+    int nrows = 0; long oob = 0;
+    bool ok(int i) { if (i < 0 || i >= (int)hull.size()) { ++oob; return false; } return true; }
+    uint32_t hull_get(int i) { return ok(i) ? hull[i] : 0; }
+    void hull_set(int i, uint32_t v) { if (ok(i)) hull[i] = v; }
+    uint32_t chg_get(int i) { return ok(i) ? chg[i] : 0; }
+    void chg_set(int i, uint32_t v) { if (ok(i)) chg[i] = v; }
     void out(int r, int c, int v) { d2[r - row0] = v; cls[r - row0] = (uint8_t)c; }
 };
 
@@ -54,10 +56,11 @@ extern "C" int emul_column_pass(const uint8_t* mask, int w, int h, int cap, int 
             int y1 = y0 + band_rows < h ? y0 + band_rows : h;
             Ctx c; c.col = inter.data() + x; c.stride = (size_t)w;
             c.hull.assign(nw, 0xdeadbeefu); c.chg.assign(nw, 0xdeadbeefu);  // poison: must be zeroed by the algorithm
-            c.d2 = cd2.data() + y0; c.cls = ccls.data() + y0; c.row0 = y0;
+            c.d2 = cd2.data() + y0; c.cls = ccls.data() + y0; c.row0 = y0; c.nrows = h;
             if (wide) { ColumnEnvelope<Ctx, true> ce(c, nw, scap); ce.run(h, y0, y1); }
             else { ColumnEnvelope<Ctx, false> ce(c, nw, scap); ce.run(h, y0, y1); }
             total += c.nld;
+            if (c.oob) return 1000 + (int)(c.oob > 1000000 ? 1000000 : c.oob);  // out-of-bounds ring/row access
         }
         for (int y = 0; y < h; ++y) { d2[(size_t)y * w + x] = cd2[y]; cls[(size_t)y * w + x] = ccls[y]; }
     }

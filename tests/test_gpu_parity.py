@@ -1,0 +1,228 @@
+"""GPU parity (run on the B200 box: pytest -m gpu). Every call goes through the C ABI (libchaqsdf_b200.so);
+the oracle (oracle/liboracle.so) and the prebuilt stock reference (oracle/_ref/libchaqref.so) are the checkers.
+Bar: bit-exact bytes and squared distances; float fields 0 ulp where D2 < 2^24 (every case below)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT
+
+sys.path.insert(0, ROOT)
+import __graft_entry__ as ge  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    p = ge.load_package()
+    p.lib()
+    return p
+
+
+def gpu_u8(pkg, img, w, h, **kw):
+    d = torch.from_numpy(np.ascontiguousarray(img)).cuda()
+    out = pkg.sdf_u8_device(d, w, h, **kw)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def random_shapes(rng, h, w):
+    yy, xx = np.mgrid[0:h, 0:w]
+    mask = np.zeros((h, w), bool)
+    for _ in range(int(rng.integers(1, 8))):
+        cy, cx, r = rng.integers(0, h), rng.integers(0, w), rng.integers(1, max(2, min(h, w) // 2))
+        m = (yy - cy) ** 2 + (xx - cx) ** 2 <= r * r
+        mask = (mask & ~m) if rng.random() < 0.3 else (mask | m)
+    return (mask * 255).astype(np.uint8)
+
+
+def test_golden_pair_host_api(pkg):
+    z = np.load(os.path.join(GOLDEN, "sample_pair.npz"))
+    out = pkg.sdf_u8(np.ascontiguousarray(z["ya"]), 200, 200, stride=2, offset=0, test_above=True, spread=100,
+                     asymmetric=True)
+    assert np.array_equal(out, z["out"])
+
+
+def test_ref_vectors(pkg):
+    z = np.load(os.path.join(GOLDEN, "ref_vectors.npz"))
+    g = np.ascontiguousarray(z["grad_ya"])
+    n = g.shape[0]
+    flags = {"default": (1, True, False), "l": (0, True, False), "n": (1, False, False), "a": (1, True, True),
+             "ln": (0, False, False), "aln": (0, False, True)}
+    for name, (off, above, asym) in flags.items():
+        for s in (7, 64):
+            got = gpu_u8(pkg, g, n, n, stride=2, offset=off, test_above=above, spread=s, asymmetric=asym)
+            assert np.array_equal(got, z[f"grad_{name}_s{s}"]), (name, s)
+            assert np.array_equal(pkg.sdf_u8(g, n, n, stride=2, offset=off, test_above=above, spread=s,
+                                             asymmetric=asym), z[f"grad_{name}_s{s}"])
+
+
+def test_small_shapes_and_edges(pkg, oracle):
+    rng = np.random.default_rng(21)
+    shapes = [(1, 1), (1, 2), (2, 1), (2, 2), (1, 33), (33, 1), (7, 513), (513, 7), (31, 31), (32, 32), (33, 33),
+              (100, 1025), (257, 300), (300, 200), (200, 300), (64, 2048)]
+    for (h, w) in shapes:
+        for kind in range(4):
+            if kind == 0:
+                img = (rng.random((h, w)) < 0.5).astype(np.uint8) * 255
+            elif kind == 1:
+                img = (rng.random((h, w)) < 0.02).astype(np.uint8) * 255
+            elif kind == 2:
+                img = random_shapes(rng, h, w)
+            else:
+                img = rng.integers(0, 256, (h, w), dtype=np.uint8)  # raw bytes: exercises the 127/128 threshold
+            for spread in (1, 3, 16, 64, 300):
+                for asym in (False, True):
+                    above = bool((kind + spread) & 1) or kind != 3
+                    got = gpu_u8(pkg, img, w, h, spread=spread, asymmetric=asym, test_above=above)
+                    want = oracle.sdf(img, w, h, spread=spread, asymmetric=asym, test_above=above)
+                    assert np.array_equal(got, want), (h, w, kind, spread, asym, int((got != want).sum()))
+
+
+def test_degenerates(pkg, oracle):
+    n = 64
+    for val in (0, 126, 127, 128, 255):
+        img = np.full((n, n), val, np.uint8)
+        for above in (True, False):
+            got = gpu_u8(pkg, img, n, n, spread=8, test_above=above)
+            assert np.array_equal(got, oracle.sdf(img, n, n, spread=8, test_above=above)), (val, above)
+    for corner in ((0, 0), (0, n - 1), (n - 1, 0), (n - 1, n - 1)):
+        img = np.zeros((n, n), np.uint8)
+        img[corner] = 255
+        for spread in (4, 100):
+            assert np.array_equal(gpu_u8(pkg, img, n, n, spread=spread), oracle.sdf(img, n, n, spread=spread))
+            assert np.array_equal(gpu_u8(pkg, 255 - img, n, n, spread=spread), oracle.sdf(255 - img, n, n, spread=spread))
+    chk = ((np.indices((n, n)).sum(0) & 1) * 255).astype(np.uint8)
+    assert np.array_equal(gpu_u8(pkg, chk, n, n, spread=5), oracle.sdf(chk, n, n, spread=5))
+    half = np.zeros((n, n), np.uint8)
+    half[:, n // 2:] = 255
+    assert np.array_equal(gpu_u8(pkg, half, n, n, spread=20), oracle.sdf(half, n, n, spread=20))
+    assert np.array_equal(gpu_u8(pkg, half.T.copy(), n, n, spread=20), oracle.sdf(half.T.copy(), n, n, spread=20))
+
+
+def test_band_sizes_do_not_change_the_result(pkg, oracle):
+    img = oracle.syn_discs(1024)
+    want = oracle.sdf(img, 1024, 1024, spread=48)
+    try:
+        for band in ("1", "17", "64", "333", "5000"):
+            os.environ["CHAQSDF_BAND_ROWS"] = band
+            assert np.array_equal(gpu_u8(pkg, img, 1024, 1024, spread=48), want), band
+    finally:
+        os.environ.pop("CHAQSDF_BAND_ROWS", None)
+
+
+def test_strided_input_and_invert(pkg, oracle):
+    rng = np.random.default_rng(4)
+    h, w = 130, 1100
+    ya = rng.integers(0, 256, (h, w, 2), dtype=np.uint8)
+    ya[20:90, 100:900, :] = 200
+    for off in (0, 1):
+        for above in (True, False):
+            got = gpu_u8(pkg, ya, w, h, stride=2, offset=off, test_above=above, spread=12)
+            assert np.array_equal(got, oracle.sdf(ya, w, h, stride=2, offset=off, test_above=above, spread=12))
+    rgba = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    got = gpu_u8(pkg, rgba, w, h, stride=4, offset=3, spread=9)
+    assert np.array_equal(got, oracle.sdf(rgba, w, h, stride=4, offset=3, spread=9))
+
+
+def test_exact_fields(pkg, oracle):
+    rng = np.random.default_rng(8)
+    for (h, w) in ((64, 64), (200, 333), (512, 512), (1, 50), (50, 1)):
+        for img in (random_shapes(rng, h, w), (rng.random((h, w)) < 0.01).astype(np.uint8) * 255,
+                    np.zeros((h, w), np.uint8), np.full((h, w), 255, np.uint8)):
+            d = torch.from_numpy(img).cuda()
+            res = pkg.sdf_fields_device(d, w, h, spread=16)
+            torch.cuda.synchronize()
+            out, sdf, din, dout = oracle.sdf(img, w, h, spread=16, fields=True)
+            assert np.array_equal(res["d2_in"].cpu().numpy(), din)
+            assert np.array_equal(res["d2_out"].cpu().numpy(), dout)
+            assert np.array_equal(res["out"].cpu().numpy(), out)
+            assert np.array_equal(res["sdf"].cpu().numpy().view(np.uint32), sdf.view(np.uint32))  # 0 ulp
+            fin = np.where(din == 2**31 - 1, np.float32(np.inf), np.sqrt(din.astype(np.float32)))
+            assert np.array_equal(res["f_in"].cpu().numpy().view(np.uint32), fin.astype(np.float32).view(np.uint32))
+
+
+def test_dist_transform_2d_dropin(pkg, oracle, ref):
+    rng = np.random.default_rng(9)
+    for n in (64, 500, 1024):
+        seeds = rng.random((n, n)) < 0.002
+        f = np.where(seeds, np.float32(0), np.float32(np.inf)).astype(np.float32)
+        got = pkg.dist_transform_2d(f.copy())
+        assert np.array_equal(got.view(np.uint32), ref.dist_transform_2d(f).view(np.uint32))  # stock build, 0 ulp
+    f = np.full((40, 70), np.inf, np.float32)  # non-square (stock build is UB here), no seed at all
+    assert np.isinf(pkg.dist_transform_2d(f.copy())).all()
+    f[3, 60] = 0
+    got = pkg.dist_transform_2d(f.copy())
+    assert np.array_equal(got.view(np.uint32), oracle.dist_transform_2d_binary(f).view(np.uint32))
+    bad = np.ones((8, 8), np.float32)  # general heights: refused, buffer untouched
+    with pytest.raises(pkg.ChaqSdfError):
+        pkg.dist_transform_2d(bad)
+    assert (bad == 1).all()
+
+
+def test_batched_glyphs(pkg, oracle):
+    rng = np.random.default_rng(12)
+    n, s = 37, 64
+    imgs = np.stack([random_shapes(rng, s, s) for _ in range(n)])
+    d = torch.from_numpy(imgs).cuda()
+    out = pkg.sdf_u8_batched_device(d, n, s, s, spread=16)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    for k in range(n):
+        assert np.array_equal(got[k], oracle.sdf(imgs[k], s, s, spread=16)), k
+
+
+def test_row_band_sharding_single_process(pkg, oracle):
+    """The multi-GPU decomposition, emulated on one GPU: each 'rank' runs pass 1 on its band, halos are copied
+    as exchange_halos would, pass 2 runs per band; the stitched result must equal the unsharded one."""
+    h, w, spread = 700, 640, 40
+    img = oracle.syn_discs(w, h)
+    want = oracle.sdf(img, w, h, spread=spread)
+    d_img = torch.from_numpy(img).cuda()
+    for world in (2, 3, 8, 32):
+        inters = {}
+        for rank in range(world):
+            r0, r1 = pkg.shard_rows(h, world, rank)
+            buf = torch.empty((r1 - r0, w), dtype=torch.int16, device="cuda")
+            pkg.rowscan_device(d_img[r0:r1], w, r1 - r0, spread, buf)
+            inters[rank] = buf
+        full = torch.cat([inters[r] for r in range(world)])
+        for rank in range(world):
+            r0, r1, ht, hb, recvs, sends = pkg.halo_plan(h, world, rank, spread)
+            buf = full[r0 - ht:r1 + hb].contiguous()
+            out = torch.empty((r1 - r0, w), dtype=torch.uint8, device="cuda")
+            pkg.envelope_device(buf, w, buf.shape[0], ht, ht + r1 - r0, spread, False, out)
+            torch.cuda.synchronize()
+            assert np.array_equal(out.cpu().numpy(), want[r0:r1]), (world, rank)
+
+
+@pytest.mark.parametrize("n,spread", [(4096, 64)])
+def test_config2_full_size(pkg, oracle, ref, n, spread):
+    img = oracle.syn_discs(n)
+    got = gpu_u8(pkg, img, n, n, spread=spread)
+    assert np.array_equal(got, oracle.sdf(img, n, n, spread=spread))
+    assert np.array_equal(got, ref.sdf_u8(img, n, n, spread=spread))  # stock OpenMP build is exact at 4096
+
+
+def test_config4_full_size(pkg, oracle):
+    n, spread = 16384, 256
+    img = oracle.syn_discs(n)
+    got = gpu_u8(pkg, img, n, n, spread=spread)
+    want = oracle.sdf(img, n, n, spread=spread)
+    assert np.array_equal(got, want)
+    # size-independent property: the transform commutes with transposition
+    gt = gpu_u8(pkg, np.ascontiguousarray(img.T), n, n, spread=spread)
+    assert np.array_equal(gt, want.T)
+
+
+def test_error_paths(pkg):
+    d = torch.zeros((8, 8), dtype=torch.uint8, device="cuda")
+    with pytest.raises(pkg.ChaqSdfError):
+        pkg.sdf_u8_device(d, 8, 8, spread=0)
+    with pytest.raises(pkg.ChaqSdfError):
+        pkg.sdf_u8_device(d, 8, 8, spread=4, workspace=torch.zeros(16, dtype=torch.uint8, device="cuda"))

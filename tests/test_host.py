@@ -73,7 +73,8 @@ def _emul_u8(L, mask, spread, asym, band, wide=0, cap=None):
     h, w = mask.shape
     d2 = np.empty((h, w), np.int32)
     cls = np.empty((h, w), np.uint8)
-    L.emul_column_pass(np.ascontiguousarray(mask), w, h, spread + 1 if cap is None else cap, band, wide, d2, cls, None)
+    rc = L.emul_column_pass(np.ascontiguousarray(mask), w, h, spread + 1 if cap is None else cap, band, wide, d2, cls, None)
+    assert rc == 0, f"out-of-bounds ring/row access in the emulated column pass (rc={rc})"
     out = np.empty((h, w), np.uint8)
     L.emul_quantise(d2, cls, h * w, spread, int(asym), out)
     return out, d2, cls
@@ -109,6 +110,11 @@ def test_emulated_discs_and_noise(emul, oracle):
     for spread, band in ((16, 0), (64, 100), (300, 0)):
         got, _, _ = _emul_u8(emul, mask, spread, False, band)
         assert np.array_equal(got, oracle.sdf(img, 384, 384, spread=spread))
+    big = oracle.syn_discs(1024)  # long stretches without sites: stale stack entries must be forgotten
+    bmask = (big > 127).astype(np.uint8)
+    for spread in (2, 33, 100):
+        got, _, _ = _emul_u8(emul, bmask, spread, False, 0)
+        assert np.array_equal(got, oracle.sdf(big, 1024, 1024, spread=spread))
     noise = oracle.syn_noise(200)
     got, _, _ = _emul_u8(emul, (noise > 127).astype(np.uint8), 8, True, 50)
     assert np.array_equal(got, oracle.sdf(noise, 200, 200, spread=8, asymmetric=True))
