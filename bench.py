@@ -171,7 +171,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- single-GPU step split into its two launches so the dominant kernel can be timed live ----
     if world == 1:
-        inter = torch.empty((h, w), dtype=torch.int16, device=dev)
+        inter = torch.empty((h, pkg.inter_row_bytes(w, SPREAD)), dtype=torch.uint8, device=dev)
         out = torch.empty((h, w), dtype=torch.uint8, device=dev)
         nb = int(pkg.lib().chaqsdf_envelope_workspace_bytes(w, h, SPREAD))
         ws = torch.empty(max(nb, 256), dtype=torch.uint8, device=dev)

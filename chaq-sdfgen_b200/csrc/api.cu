@@ -15,6 +15,8 @@
 #include "../../include/chaqsdf.h"
 #include "envelope.cuh"
 #include "rowscan.cuh"
+#include "rowscan8.cuh"
+#include "sweep.cuh"
 
 using namespace chaq;
 
@@ -34,6 +36,15 @@ int fail(int code, const std::string& msg) {
             return fail(CHAQSDF_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));          \
     } while (0)
 
+#define CQ_LAUNCHED(what, grid, smem)                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = cudaGetLastError();                                                            \
+        if (e_ != cudaSuccess)                                                                          \
+            return fail(CHAQSDF_ERR_CUDA, std::string(what) + " launch (grid " + std::to_string(grid) + ", smem " +  \
+                                              std::to_string(smem) + "): " + cudaGetErrorString(e_));   \
+        g_launches.fetch_add(1, std::memory_order_relaxed);                                             \
+    } while (0)
+
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct DevInfo {
@@ -42,7 +53,12 @@ struct DevInfo {
 };
 std::mutex g_mu;
 std::map<int, DevInfo> g_dev;
-std::map<std::tuple<int, size_t, int>, QuantTable*> g_tables;
+struct Tables {
+    QuantTable* dq = nullptr;   // device copies
+    LevelTable* dl = nullptr;
+    LevelTable hl;              // host copy (cap_eff decides the geometry of the banded path)
+};
+std::map<std::tuple<int, size_t, int>, Tables> g_tables;
 
 int device_info(DevInfo* out) {
     int dev = 0;
@@ -61,7 +77,7 @@ int device_info(DevInfo* out) {
 
 // per-(device, spread, asymmetric) quantisation thresholds, built on the host from the reference's float
 // formula (tables.h) and kept on the device for the life of the process.
-int get_table(size_t spread, int asymmetric, const QuantTable** out) {
+int get_table(size_t spread, int asymmetric, const Tables** out) {
     int dev = 0;
     CQ_CUDA(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(g_mu);
@@ -70,12 +86,15 @@ int get_table(size_t spread, int asymmetric, const QuantTable** out) {
     if (it == g_tables.end()) {
         QuantTable h;
         build_quant_table(spread, asymmetric, &h);
-        QuantTable* d = nullptr;
-        CQ_CUDA(cudaMalloc(&d, sizeof(QuantTable)));
-        CQ_CUDA(cudaMemcpy(d, &h, sizeof(QuantTable), cudaMemcpyHostToDevice));
-        it = g_tables.emplace(key, d).first;
+        Tables t;
+        build_level_table(h, &t.hl);
+        CQ_CUDA(cudaMalloc(&t.dq, sizeof(QuantTable)));
+        CQ_CUDA(cudaMemcpy(t.dq, &h, sizeof(QuantTable), cudaMemcpyHostToDevice));
+        CQ_CUDA(cudaMalloc(&t.dl, sizeof(LevelTable)));
+        CQ_CUDA(cudaMemcpy(t.dl, &t.hl, sizeof(LevelTable), cudaMemcpyHostToDevice));
+        it = g_tables.emplace(key, t).first;
     }
-    *out = it->second;
+    *out = &it->second;
     return CHAQSDF_OK;
 }
 
@@ -90,7 +109,15 @@ int check_dims(size_t w, size_t h, size_t spread) {
 
 int cap_for(size_t spread) { return spread + 1 > 0x7fff ? 0x7fff : (int)(spread + 1); }
 
-// launch geometry of pass 2
+// ---- intermediate formats --------------------------------------------------------------------------------
+// banded (spread <= 256): per row [Wp bytes g8 | Wp/8 bytes class bits], Wp = w rounded up to 128
+// general               : per row w uint16 (bit 15 class, bits 0..14 row distance saturated at spread+1)
+bool banded(size_t spread) { return spread <= 256; }
+int banded_wp(size_t w) { return (int)align_up(w, 128); }
+size_t banded_rs(size_t w) { return (size_t)banded_wp(w) + (size_t)banded_wp(w) / 8; }
+size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w) : w * sizeof(uint16_t); }
+
+// launch geometry of the general pass 2
 struct EnvPlan {
     int cap, nw, band_rows, nbands;
     bool wide, global_ring;
@@ -135,8 +162,7 @@ int launch_env_t(const EnvPlan& pl, const EnvParams& p, cudaStream_t st) {
     if (pl.smem_bytes > 48 * 1024)
         CQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
     k<<<pl.grid, kEnvThreads, pl.smem_bytes, st>>>(p);
-    CQ_CUDA(cudaGetLastError());
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CQ_LAUNCHED("envelope_kernel", pl.grid.x * pl.grid.y * pl.grid.z, pl.smem_bytes);
     return CHAQSDF_OK;
 }
 
@@ -163,8 +189,139 @@ int launch_rowscan(const uint8_t* d_img, size_t w, size_t rows, size_t stride, s
     const size_t smem = (size_t)kRowWarps * rp.nwords * sizeof(uint32_t);
     const unsigned blocks = (unsigned)((rows + kRowWarps - 1) / kRowWarps);
     rowscan_kernel<<<blocks, kRowWarps * 32, smem, st>>>(rp);
-    CQ_CUDA(cudaGetLastError());
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CQ_LAUNCHED("rowscan_kernel", blocks, smem);
+    return CHAQSDF_OK;
+}
+
+// ---- banded path -------------------------------------------------------------------------------------------
+int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
+                    size_t spread, uint8_t* d_inter, cudaStream_t st) {
+    RowScan8Params rp;
+    rp.img = d_img; rp.inter = d_inter; rp.rows = (long long)rows; rp.rs = (long long)banded_rs(w);
+    rp.wp = banded_wp(w); rp.w = (int)w; rp.stride = (int)stride; rp.offset = (int)offset;
+    rp.above = test_above ? 1 : 0; rp.cap = spread + 1 > 256 ? 256 : (int)(spread + 1);
+    rp.nwords = (int)((w + 31) / 32);
+    const size_t smem = (size_t)kRow8Warps * (rp.nwords + 1) * sizeof(uint32_t);
+    const unsigned blocks = (unsigned)((rows + kRow8Warps - 1) / kRow8Warps);
+    rowscan8_kernel<<<blocks, kRow8Warps * 32, smem, st>>>(rp);
+    CQ_LAUNCHED("rowscan8_kernel", blocks, smem);
+    return CHAQSDF_OK;
+}
+
+struct SweepGeom {
+    int wpc = 0;         // warps per CTA
+    int ctas_per_sm = 0;
+};
+std::map<std::pair<int, int>, SweepGeom> g_sweep_geom;  // (device, ring blocks) -> best CTA shape
+
+std::map<std::pair<int, int>, size_t> g_sweep_smem_limit;  // (device, wpc) -> opt-in limit set so far (g_mu held)
+
+// The opt-in shared-memory limit is per kernel instance and sticky: only ever raise it.
+template <int WPC>
+int sweep_raise_limit(int dev, size_t smem) {
+    size_t& cur = g_sweep_smem_limit[std::make_pair(dev, WPC)];
+    if (smem > cur) {
+        CQ_CUDA(cudaFuncSetAttribute(sweep_kernel<WPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cur = smem;
+    }
+    return CHAQSDF_OK;
+}
+int sweep_raise_limit_any(int wpc, int dev, size_t smem) {
+    switch (wpc) {
+        case 1: return sweep_raise_limit<1>(dev, smem);
+        case 2: return sweep_raise_limit<2>(dev, smem);
+        case 4: return sweep_raise_limit<4>(dev, smem);
+        case 5: return sweep_raise_limit<5>(dev, smem);
+        case 8: return sweep_raise_limit<8>(dev, smem);
+        default: return sweep_raise_limit<10>(dev, smem);
+    }
+}
+template <int WPC>
+int sweep_occupancy(int dev, size_t smem, int* ctas) {
+    if (int rc = sweep_raise_limit<WPC>(dev, smem)) return rc;
+    CQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas, sweep_kernel<WPC>, WPC * 32, smem));
+    return CHAQSDF_OK;
+}
+
+int sweep_geometry(int nb, SweepGeom* out) {
+    DevInfo di;
+    if (int rc = device_info(&di)) return rc;
+    int dev = 0;
+    CQ_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto key = std::make_pair(dev, nb);
+    auto it = g_sweep_geom.find(key);
+    if (it == g_sweep_geom.end()) {
+        const size_t per_warp = (size_t)nb * 1280;
+        SweepGeom best;
+        int best_warps = 0;
+        const int cand[6] = {1, 2, 4, 5, 8, 10};
+        for (int i = 0; i < 6; ++i) {
+            const int wpc = cand[i];
+            const size_t smem = per_warp * wpc;
+            if (smem > (size_t)di.max_smem_optin) continue;
+            int ctas = 0, rc = 0;
+            switch (wpc) {
+                case 1: rc = sweep_occupancy<1>(dev, smem, &ctas); break;
+                case 2: rc = sweep_occupancy<2>(dev, smem, &ctas); break;
+                case 4: rc = sweep_occupancy<4>(dev, smem, &ctas); break;
+                case 5: rc = sweep_occupancy<5>(dev, smem, &ctas); break;
+                case 8: rc = sweep_occupancy<8>(dev, smem, &ctas); break;
+                default: rc = sweep_occupancy<10>(dev, smem, &ctas); break;
+            }
+            if (rc) return rc;
+            if (ctas * wpc > best_warps) { best_warps = ctas * wpc; best.wpc = wpc; best.ctas_per_sm = ctas; }
+        }
+        if (const char* e = getenv("CHAQSDF_SWEEP_WPC")) {  // tuning override: "wpc,ctas"
+            int a = 0, b = 0;
+            if (sscanf(e, "%d,%d", &a, &b) == 2 && a > 0 && b > 0) { best.wpc = a; best.ctas_per_sm = b; best_warps = a * b; }
+        }
+        if (best_warps == 0) return fail(CHAQSDF_ERR_CUDA, "banded pass 2 does not fit in shared memory");
+        it = g_sweep_geom.emplace(key, best).first;
+    }
+    *out = it->second;
+    return CHAQSDF_OK;
+}
+
+int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
+                 const Tables* tab, uint8_t* d_out, cudaStream_t st) {
+    DevInfo di;
+    if (int rc = device_info(&di)) return rc;
+    SweepParams p{};
+    p.inter = d_inter; p.out = d_out; p.table = tab->dl;
+    p.rs = (long long)banded_rs(w); p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
+    p.out_begin = (int)out_begin; p.out_end = (int)out_end;
+    p.ncg = (int)((w + 31) / 32);
+    p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2; p.nb = sweep_ring_blocks(p.L);
+    const long long out_rows = (long long)(out_end - out_begin);
+    p.total_rows = (long long)n_img * p.ncg * out_rows;
+    SweepGeom g;
+    if (int rc = sweep_geometry(p.nb, &g)) return rc;
+    const long long slots = (long long)di.sms * g.ctas_per_sm * g.wpc;
+    long long run = (p.total_rows + slots - 1) / slots;
+    long long min_run = 4LL * p.L > 128 ? 4LL * p.L : 128;  // keep the 2L rows of re-read context under ~50 %
+    if (min_run > out_rows) min_run = out_rows;
+    if (run < min_run) run = min_run;
+    if (const char* e = getenv("CHAQSDF_BAND_ROWS")) run = atoll(e) > 0 ? atoll(e) : run;
+    p.rows_per_warp = run;
+    const long long nwarps = (p.total_rows + run - 1) / run;
+    const unsigned grid = (unsigned)((nwarps + g.wpc - 1) / g.wpc);
+    const size_t smem = (size_t)p.nb * 1280 * g.wpc;
+    {
+        int dev = 0;
+        CQ_CUDA(cudaGetDevice(&dev));
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (int rc = sweep_raise_limit_any(g.wpc, dev, smem)) return rc;
+    }
+    switch (g.wpc) {
+        case 1: sweep_kernel<1><<<grid, 32, smem, st>>>(p); break;
+        case 2: sweep_kernel<2><<<grid, 64, smem, st>>>(p); break;
+        case 4: sweep_kernel<4><<<grid, 128, smem, st>>>(p); break;
+        case 5: sweep_kernel<5><<<grid, 160, smem, st>>>(p); break;
+        case 8: sweep_kernel<8><<<grid, 256, smem, st>>>(p); break;
+        default: sweep_kernel<10><<<grid, 320, smem, st>>>(p); break;
+    }
+    CQ_LAUNCHED("sweep_kernel<" + std::to_string(g.wpc) + ">", grid, smem);
     return CHAQSDF_OK;
 }
 
@@ -180,12 +337,18 @@ void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 // ------------------------------------------------------------------------------------------------
 extern "C" {
 
-int chaqsdf_version(void) { return 100; }
+int chaqsdf_version(void) { return 110; }
 const char* chaqsdf_last_error_string(void) { return g_err.c_str(); }
 unsigned long long chaqsdf_launch_count(void) { return g_launches.load(); }
 
+size_t chaqsdf_inter_row_bytes(size_t w, size_t spread) {
+    if (w == 0 || w > CHAQSDF_MAX_DIM || spread == 0) return 0;
+    return inter_row_bytes(w, spread);
+}
+
 size_t chaqsdf_batched_workspace_bytes(size_t n, size_t w, size_t h, size_t spread) {
     if (check_dims(w, h, spread) || n == 0) return 0;
+    if (banded(spread)) return align_up(n * h * banded_rs(w), 256);
     EnvPlan pl;
     if (plan_envelope(w, h, h, n, cap_for(spread), &pl)) return 0;
     return align_up(n * w * h * sizeof(uint16_t), 256) + pl.ring_bytes;
@@ -195,6 +358,7 @@ size_t chaqsdf_workspace_bytes(size_t w, size_t h, size_t spread) {
 }
 size_t chaqsdf_envelope_workspace_bytes(size_t w, size_t buf_rows, size_t spread) {
     if (check_dims(w, buf_rows, spread)) return 0;
+    if (banded(spread)) return 0;
     EnvPlan pl;
     if (plan_envelope(w, buf_rows, buf_rows, 1, cap_for(spread), &pl)) return 0;
     return pl.ring_bytes;
@@ -207,31 +371,38 @@ size_t chaqsdf_fields_workspace_bytes(size_t w, size_t h) {
 }
 
 int chaqsdf_rowscan_device(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
-                           size_t spread, uint16_t* d_inter, void* stream) {
+                           size_t spread, void* d_inter, void* stream) {
     if (!d_img || !d_inter) return fail(CHAQSDF_ERR_ARG, "null pointer");
     if (w == 0 || rows == 0) return fail(CHAQSDF_ERR_ARG, "empty image");
     if (w > CHAQSDF_MAX_DIM) return fail(CHAQSDF_ERR_ARG, "image side exceeds 32768");
     if (spread == 0) return fail(CHAQSDF_ERR_ARG, "spread must be a positive integer");
     if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
-    return launch_rowscan(d_img, w, rows, stride, offset, test_above, cap_for(spread), d_inter, (cudaStream_t)stream);
+    if (banded(spread))
+        return launch_rowscan8(d_img, w, rows, stride, offset, test_above, spread, (uint8_t*)d_inter, (cudaStream_t)stream);
+    return launch_rowscan(d_img, w, rows, stride, offset, test_above, cap_for(spread), (uint16_t*)d_inter,
+                          (cudaStream_t)stream);
 }
 
-int chaqsdf_envelope_device(const uint16_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
+int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
                             size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
                             void* stream) {
     if (!d_inter || !d_out) return fail(CHAQSDF_ERR_ARG, "null pointer");
     if (int rc = check_dims(w, buf_rows, spread)) return rc;
     if (out_begin >= out_end || out_end > buf_rows) return fail(CHAQSDF_ERR_ARG, "bad output row range");
+    const Tables* tab;
+    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
+    if (banded(spread)) {
+        if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
+        return launch_sweep((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, (cudaStream_t)stream);
+    }
     EnvPlan pl;
     if (int rc = plan_envelope(w, buf_rows, out_end - out_begin, 1, cap_for(spread), &pl)) return rc;
     if (pl.ring_bytes > workspace_bytes || (pl.ring_bytes && !d_workspace))
         return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
-    const QuantTable* tab;
-    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     EnvParams p{};
-    p.inter = d_inter; p.w = (int)w; p.buf_rows = (int)buf_rows;
+    p.inter = (const uint16_t*)d_inter; p.w = (int)w; p.buf_rows = (int)buf_rows;
     p.out_begin = (int)out_begin; p.out_end = (int)out_end; p.band_rows = pl.band_rows;
-    p.cap = pl.cap; p.nw = pl.nw; p.table = tab; p.out = d_out; p.gring = (uint32_t*)d_workspace;
+    p.cap = pl.cap; p.nw = pl.nw; p.table = tab->dq; p.out = d_out; p.gring = (uint32_t*)d_workspace;
     return launch_env(pl, p, false, (cudaStream_t)stream);
 }
 
@@ -242,19 +413,25 @@ int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t 
     if (n == 0) return fail(CHAQSDF_ERR_ARG, "empty batch");
     if (int rc = check_dims(w, h, spread)) return rc;
     if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
+    const Tables* tab;
+    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (banded(spread)) {
+        if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
+        if (workspace_bytes < align_up(n * h * banded_rs(w), 256)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+        if (int rc = launch_rowscan8(d_imgs, w, n * h, stride, offset, test_above, spread, (uint8_t*)d_workspace, st)) return rc;
+        return launch_sweep((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, st);
+    }
     const int cap = cap_for(spread);
     EnvPlan pl;
     if (int rc = plan_envelope(w, h, h, n, cap, &pl)) return rc;
     const size_t inter_bytes = align_up(n * w * h * sizeof(uint16_t), 256);
     if (workspace_bytes < inter_bytes + pl.ring_bytes) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
-    const QuantTable* tab;
-    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     uint16_t* inter = (uint16_t*)d_workspace;
-    cudaStream_t st = (cudaStream_t)stream;
     if (int rc = launch_rowscan(d_imgs, w, n * h, stride, offset, test_above, cap, inter, st)) return rc;
     EnvParams p{};
     p.inter = inter; p.w = (int)w; p.buf_rows = (int)h; p.out_begin = 0; p.out_end = (int)h;
-    p.band_rows = pl.band_rows; p.cap = cap; p.nw = pl.nw; p.table = tab; p.out = d_out;
+    p.band_rows = pl.band_rows; p.cap = cap; p.nw = pl.nw; p.table = tab->dq; p.out = d_out;
     p.gring = (uint32_t*)((char*)d_workspace + inter_bytes);
     return launch_env(pl, p, false, st);
 }
@@ -279,14 +456,14 @@ int chaqsdf_fields_device(const uint8_t* d_img, size_t w, size_t h, size_t strid
     if (int rc = plan_envelope(w, h, h, 1, cap, &pl)) return rc;
     const size_t inter_bytes = align_up(w * h * sizeof(uint16_t), 256);
     if (workspace_bytes < inter_bytes + pl.ring_bytes) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
-    const QuantTable* tab;
+    const Tables* tab;
     if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     uint16_t* inter = (uint16_t*)d_workspace;
     cudaStream_t st = (cudaStream_t)stream;
     if (int rc = launch_rowscan(d_img, w, h, stride, offset, test_above, cap, inter, st)) return rc;
     EnvParams p{};
     p.inter = inter; p.w = (int)w; p.buf_rows = (int)h; p.out_begin = 0; p.out_end = (int)h;
-    p.band_rows = pl.band_rows; p.cap = cap; p.nw = pl.nw; p.table = tab; p.out = d_out;
+    p.band_rows = pl.band_rows; p.cap = cap; p.nw = pl.nw; p.table = tab->dq; p.out = d_out;
     p.d2_in = d_d2_in; p.d2_out = d_d2_out; p.f_in = d_f_in; p.f_out = d_f_out; p.sdf = d_sdf;
     p.gring = (uint32_t*)((char*)d_workspace + inter_bytes);
     return launch_env(pl, p, true, st);

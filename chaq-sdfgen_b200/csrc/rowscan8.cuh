@@ -1,0 +1,155 @@
+// rowscan8.cuh -- pass 1, banded fast path (spread <= 256): threshold + per-row distance to the nearest
+// pixel of the other class, 8 bits per pixel plus a class bit-plane.
+//
+// Replaces, fused into one kernel and for both fields at once:
+//   transform_img_to_bool    reference openmp/sdfgen.c:52-62   (px > 127 / px < 127 on a strided byte image)
+//   transform_bool_to_float  reference openmp/sdfgen.c:65-72   ({0,INF} seeds for each field)
+//   dist_transform_axis #1   reference openmp/df.c:130 -> df.c:29-97 (for {0,INF} input the lower envelope
+//                            along a row is (x - nearest seed)^2, i.e. a run-length scan)
+// Output record per row (see sweep.cuh): Wp bytes g8 = min(G, C) - 1, then Wp/32 words of class bits
+// (bit = 1: inside, the reference's `true`). G = distance along the row to the nearest pixel of the OTHER
+// class. The distance is class-agnostic: it is the distance to the nearest class change, so one pair of
+// ramps serves both fields.
+//
+// Mapping: one warp per row, 8 rows per CTA. Phase A turns the row into a bit string in shared memory
+// (16 pixels per lane per 128-bit load on the fast path, ballot on the generic path). Phase B gives each lane
+// one 32-pixel word: the nearest change outside the word comes from warp ballots plus a carry from earlier
+// 1024-pixel chunks and a one-chunk look-ahead; inside the word two 32-step ramps finish the job in registers,
+// and the 32 result bytes leave as two 128-bit stores.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "rowscan.cuh"  // class_nibble, kFar
+
+namespace chaq {
+
+constexpr int kRow8Warps = 8;
+
+struct RowScan8Params {
+    const uint8_t* img;
+    uint8_t* inter;      // records
+    long long rows;
+    long long rs;        // record stride
+    int wp;              // padded width
+    int w;
+    int stride, offset;
+    int above;
+    int cap;             // C_row = min(spread+1, 256): g8 = min(G, cap) - 1
+    int nwords;          // ceil(w/32)
+};
+
+__global__ void __launch_bounds__(kRow8Warps * 32) rowscan8_kernel(RowScan8Params p) {
+    extern __shared__ uint32_t s_bits8[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long row = (long long)blockIdx.x * kRow8Warps + warp;
+    if (row >= p.rows) return;  // whole warp leaves together; no block-level barrier is used below
+    uint32_t* bits = s_bits8 + warp * (p.nwords + 1);
+    const int w = p.w;
+    const bool above = p.above != 0;
+    const uint8_t* src = p.img + (size_t)row * (size_t)w * (size_t)p.stride + (size_t)p.offset;
+
+    // ---------------- phase A: class bits of the row -> shared memory ----------------
+    int word0 = 0;
+    if (p.stride == 1 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+        const int nfull = w >> 9;  // chunks of 512 pixels: 16 per lane
+        const uint4* s4 = reinterpret_cast<const uint4*>(src);
+        for (int i = 0; i < nfull; ++i) {
+            uint4 q = __ldg(s4 + (size_t)i * 32 + lane);
+            uint32_t m = class_nibble(q.x, above) | (class_nibble(q.y, above) << 4) |
+                         (class_nibble(q.z, above) << 8) | (class_nibble(q.w, above) << 12);
+            uint32_t o = __shfl_xor_sync(0xffffffffu, m, 1);
+            if (!(lane & 1)) bits[i * 16 + (lane >> 1)] = m | (o << 16);
+        }
+        word0 = nfull * 16;
+    }
+    for (int wi = word0; wi < p.nwords; ++wi) {
+        int x = wi * 32 + lane;
+        bool c = false;
+        if (x < w) {
+            uint8_t px = __ldg(src + (size_t)x * (size_t)p.stride);
+            c = above ? px > 127 : px < 127;
+        }
+        uint32_t b = __ballot_sync(0xffffffffu, c);
+        if (lane == 0) bits[wi] = b;
+    }
+    __syncwarp();
+
+    // ---------------- phase B: distances ----------------
+    const int cap = p.cap;
+    uint8_t* rec = p.inter + (size_t)row * (size_t)p.rs;
+    uint32_t* crec = reinterpret_cast<uint32_t*>(rec + p.wp);
+    const uint32_t lt = (1u << lane) - 1u, gt = lane == 31 ? 0u : (0xFFFFFFFEu << lane);
+    int carryL = -kFar;  // last pixel of earlier chunks that has a class change immediately to its left
+    const int nchunks = (p.nwords + 31) >> 5;
+    for (int ch = 0; ch < nchunks; ++ch) {
+        const int wi = ch * 32 + lane;
+        const int x0 = wi * 32;
+        int nvalid = w - x0;
+        nvalid = nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
+        int evalid = w - 1 - x0;  // positions b whose right neighbour b+1 exists
+        evalid = evalid < 0 ? 0 : (evalid > 32 ? 32 : evalid);
+        const uint32_t v = wi < p.nwords ? bits[wi] : 0u;
+        const uint32_t nbit = wi + 1 < p.nwords ? (bits[wi + 1] & 1u) : 0u;
+        const uint32_t pbit = (wi > 0 && wi < p.nwords) ? (bits[wi - 1] >> 31) : (v & 1u);
+        const uint32_t em = evalid == 32 ? 0xFFFFFFFFu : ((1u << evalid) - 1u);
+        const uint32_t R = (v ^ ((v >> 1) | (nbit << 31))) & em;     // bit b: classes of b and b+1 differ
+        const uint32_t Lw = nvalid ? ((R << 1) | ((pbit ^ v) & 1u)) : 0u;  // bit b: classes of b-1 and b differ
+        const uint32_t BL = __ballot_sync(0xffffffffu, Lw != 0), BR = __ballot_sync(0xffffffffu, R != 0);
+        const int lastL = Lw ? x0 + (31 - __clz(Lw)) : -kFar;
+        const int firstR = R ? x0 + __ffs(R) - 1 : kFar;
+
+        // look-ahead: the first pixel of the next chunk whose class differs from this chunk's last pixel
+        int look = 2 * kFar;
+        if (ch + 1 < nchunks) {  // uniform; one chunk ahead is always enough (1024 >= cap)
+            const uint32_t lastv = __shfl_sync(0xffffffffu, v, 31);
+            const uint32_t flip = (lastv >> 31) ? 0xFFFFFFFFu : 0u;
+            const int wj = wi + 32;
+            int nv = w - wj * 32;
+            nv = nv < 0 ? 0 : (nv > 32 ? 32 : nv);
+            const uint32_t m2 = nv == 32 ? 0xFFFFFFFFu : ((1u << nv) - 1u);
+            const uint32_t d2 = wj < p.nwords ? ((bits[wj] ^ flip) & m2) : 0u;
+            const uint32_t C = __ballot_sync(0xffffffffu, d2 != 0);
+            const int f = d2 ? wj * 32 + __ffs(d2) - 2 : kFar;  // the pixel left of the first differing one
+            const int g = __shfl_sync(0xffffffffu, f, C ? __ffs(C) - 1 : 0);
+            if (C) look = g;
+        }
+        const uint32_t pl = BL & lt, nr = BR & gt;
+        const int sl = __shfl_sync(0xffffffffu, lastL, pl ? 31 - __clz(pl) : 0);
+        const int sr = __shfl_sync(0xffffffffu, firstR, nr ? __ffs(nr) - 1 : 0);
+        const int PL = pl ? sl : carryL;
+        const int PR = nr ? sr : look;
+        const int tl = __shfl_sync(0xffffffffu, lastL, BL ? 31 - __clz(BL) : 0);
+        if (BL) carryL = tl;
+
+        if (nvalid > 0) {
+            int dl[32];
+            int z = x0 - PL + 1;
+#pragma unroll
+            for (int b = 0; b < 32; ++b) {
+                z = ((Lw >> b) & 1u) ? 1 : z;
+                dl[b] = z;
+                z += 1;
+            }
+            int y = PR - (x0 + 31) + 1;
+            uint32_t packed[8];
+#pragma unroll
+            for (int b = 31; b >= 0; --b) {
+                y = ((R >> b) & 1u) ? 1 : y;
+                const int m = min(min(dl[b], y), cap) - 1;
+                if ((b & 3) == 3) packed[b >> 2] = (uint32_t)m << 24; else packed[b >> 2] |= (uint32_t)m << (8 * (b & 3));
+                y += 1;
+            }
+            if (nvalid < 32) {  // pixels past the end of the row: "none"
+#pragma unroll
+                for (int b = 0; b < 32; ++b)
+                    if (b >= nvalid) packed[b >> 2] = (packed[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | ((uint32_t)(cap - 1) << (8 * (b & 3)));
+            }
+            uint4* d4 = reinterpret_cast<uint4*>(rec + x0);
+            d4[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+            d4[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+            crec[wi] = v;
+        }
+    }
+}
+
+}  // namespace chaq

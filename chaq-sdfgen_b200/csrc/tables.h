@@ -112,3 +112,50 @@ inline void build_quant_table(size_t spread, int asymmetric, QuantTable* q) {
 }
 
 }  // namespace chaq
+
+// ---- unified level tables for the banded (fast) path ------------------------------------------------------
+// For class c (1 = inside) the byte is a monotone step function of the clamped squared distance; written as
+// a level m in [0,255] that never decreases with D2:
+//     m(c, D2) = max { m : thr[c][m] <= D2 },   byte = c ? m : 255 - m
+//   thr[1][m] = tin[m]          (inside : byte = m)
+//   thr[0][m] = tout[255 - m]   (outside: byte = 255 - m)
+// thr[c][0] = 0 and thr[c][256] = kBig (sentinel). cap_eff is the smallest integer C such that every D2 >= C*C
+// gives the saturated byte of both classes: pixels (or row distances) that far away need not be told apart,
+// so the banded path only looks C-1 rows up and down and only keeps row distances below C.
+namespace chaq {
+
+struct LevelTable {
+    int32_t thr[2][260];
+    int32_t cap_eff;   // C
+    int32_t c2;        // C*C: squared distances are clamped here before the look-up
+    int32_t pad[2];
+};
+
+inline void build_level_table(const QuantTable& q, LevelTable* t) {
+    int64_t last = 1;  // largest finite threshold of either class
+    for (int m = 0; m <= 255; ++m) {
+        t->thr[1][m] = q.tin[m];
+        t->thr[0][m] = q.tout[255 - m];
+        if (q.tin[m] != kBig && q.tin[m] > last) last = q.tin[m];
+        if (q.tout[255 - m] != kBig && q.tout[255 - m] > last) last = q.tout[255 - m];
+    }
+    for (int m = 256; m < 260; ++m) t->thr[0][m] = t->thr[1][m] = kBig;
+    t->thr[0][0] = t->thr[1][0] = 0;
+    int64_t c = 1;
+    while (c * c < last) ++c;
+    t->cap_eff = (int32_t)c;
+    t->c2 = (int32_t)(c * c);
+    t->pad[0] = t->pad[1] = 0;
+}
+
+// plain search, for the host emulation and for re-synchronising after a class change
+CQ_HD int level_of(const int32_t* thr, int d2c) {
+    int lo = 0, hi = 255;  // invariant: thr[lo] <= d2c
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (thr[mid] <= d2c) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+}  // namespace chaq

@@ -28,6 +28,7 @@ def build_library(force=False):
 SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "dist_transform_2d",
            "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
+           "chaqsdf_inter_row_bytes",
            "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
            "chaqsdf_fields_device"]
 
@@ -52,6 +53,8 @@ def lib():
     L.chaqsdf_batched_workspace_bytes.restype = sz
     L.chaqsdf_envelope_workspace_bytes.argtypes = [sz, sz, sz]
     L.chaqsdf_envelope_workspace_bytes.restype = sz
+    L.chaqsdf_inter_row_bytes.argtypes = [sz, sz]
+    L.chaqsdf_inter_row_bytes.restype = sz
     L.chaqsdf_fields_workspace_bytes.argtypes = [sz, sz]
     L.chaqsdf_fields_workspace_bytes.restype = sz
     L.chaqsdf_u8_device.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp, sz, vp]
@@ -138,6 +141,11 @@ def sdf_u8_batched_device(d_imgs, n, w, h, stride=1, offset=0, test_above=True, 
                                            int(asymmetric), _ptr(out), _ptr(workspace), workspace.numel(),
                                            _stream_ptr(stream)))
     return out
+
+
+def inter_row_bytes(w, spread):
+    """Bytes per image row of the opaque intermediate between the two passes."""
+    return int(lib().chaqsdf_inter_row_bytes(w, spread))
 
 
 def rowscan_device(d_img, w, rows, spread, d_inter, stride=1, offset=0, test_above=True, stream=None):
@@ -232,7 +240,7 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
     if state.get("key") != key:
         state.clear()
         state["key"] = key
-        state["inter"] = torch.empty((buf_rows, w), dtype=torch.int16, device=dev)
+        state["inter"] = torch.empty((buf_rows, inter_row_bytes(w, spread)), dtype=torch.uint8, device=dev)
         state["out"] = torch.empty((rows, w), dtype=torch.uint8, device=dev)
         nb = int(lib().chaqsdf_envelope_workspace_bytes(w, buf_rows, spread))
         state["ws"] = _workspace(nb, dev) if nb else None

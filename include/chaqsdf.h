@@ -74,17 +74,22 @@ int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t 
                               size_t workspace_bytes, void* stream);
 
 /* ---- the two passes, for row-band sharding --------------------------------------------------------
- * Pass 1 (rows are independent): threshold + per-row distance to the nearest opposite-class pixel,
- * saturated at spread+1, one uint16 per pixel (bit 15 = class, bits 0..14 = distance).
- *   d_img: `rows` rows of the image band; d_inter: uint16[rows*w]. */
+ * The intermediate between the passes is an opaque buffer of `rows` records of
+ * chaqsdf_inter_row_bytes(w, spread) bytes each, one record per image row, rows contiguous (so a run of rows
+ * can be handed to another GPU as one block). Its content depends on spread only (not on asymmetric):
+ *   spread <= 256: w (rounded up to 128) bytes of min(row distance, 256) - 1, then 1 class bit per pixel;
+ *   otherwise    : one uint16 per pixel (bit 15 = class, bits 0..14 = row distance saturated at spread+1).
+ * "row distance" = distance along the row to the nearest pixel of the other class.
+ * Pass 1 (rows are independent): threshold + row distances for `rows` rows of an image band. */
+size_t chaqsdf_inter_row_bytes(size_t w, size_t spread);
 int chaqsdf_rowscan_device(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset,
-                           int test_above, size_t spread, uint16_t* d_inter, void* stream);
+                           int test_above, size_t spread, void* d_inter, void* stream);
 /* Pass 2 (columns; needs `spread` rows of context above and below each output row, or the image edge):
- *   d_inter: uint16[buf_rows*w], any contiguous run of image rows; output rows [out_begin, out_end) of
- *   that buffer are written to d_out[(r-out_begin)*w + x]. Rows the buffer does not hold are treated as
- *   absent, which is exact when the buffer reaches the image edge or >= spread rows beyond the outputs. */
+ *   d_inter: buf_rows records, any contiguous run of image rows; output rows [out_begin, out_end) of that
+ *   buffer are written to d_out[(r-out_begin)*w + x]. Rows the buffer does not hold are treated as absent,
+ *   which is exact when the buffer reaches the image edge or >= spread rows beyond the outputs. */
 size_t chaqsdf_envelope_workspace_bytes(size_t w, size_t buf_rows, size_t spread);
-int chaqsdf_envelope_device(const uint16_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
+int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
                             size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace,
                             size_t workspace_bytes, void* stream);
 

@@ -180,25 +180,25 @@ def test_batched_glyphs(pkg, oracle):
 def test_row_band_sharding_single_process(pkg, oracle):
     """The multi-GPU decomposition, emulated on one GPU: each 'rank' runs pass 1 on its band, halos are copied
     as exchange_halos would, pass 2 runs per band; the stitched result must equal the unsharded one."""
-    h, w, spread = 700, 640, 40
-    img = oracle.syn_discs(w, h)
-    want = oracle.sdf(img, w, h, spread=spread)
-    d_img = torch.from_numpy(img).cuda()
-    for world in (2, 3, 8, 32):
-        inters = {}
-        for rank in range(world):
-            r0, r1 = pkg.shard_rows(h, world, rank)
-            buf = torch.empty((r1 - r0, w), dtype=torch.int16, device="cuda")
-            pkg.rowscan_device(d_img[r0:r1], w, r1 - r0, spread, buf)
-            inters[rank] = buf
-        full = torch.cat([inters[r] for r in range(world)])
-        for rank in range(world):
-            r0, r1, ht, hb, recvs, sends = pkg.halo_plan(h, world, rank, spread)
-            buf = full[r0 - ht:r1 + hb].contiguous()
-            out = torch.empty((r1 - r0, w), dtype=torch.uint8, device="cuda")
-            pkg.envelope_device(buf, w, buf.shape[0], ht, ht + r1 - r0, spread, False, out)
-            torch.cuda.synchronize()
-            assert np.array_equal(out.cpu().numpy(), want[r0:r1]), (world, rank)
+    for (h, w, spread) in ((700, 640, 40), (900, 333, 300)):  # banded and general intermediate
+      img = oracle.syn_discs(w, h)
+      want = oracle.sdf(img, w, h, spread=spread)
+      d_img = torch.from_numpy(img).cuda()
+      for world in (2, 3, 8, 32):
+          inters = {}
+          for rank in range(world):
+              r0, r1 = pkg.shard_rows(h, world, rank)
+              buf = torch.empty((r1 - r0, pkg.inter_row_bytes(w, spread)), dtype=torch.uint8, device="cuda")
+              pkg.rowscan_device(d_img[r0:r1], w, r1 - r0, spread, buf)
+              inters[rank] = buf
+          full = torch.cat([inters[r] for r in range(world)])
+          for rank in range(world):
+              r0, r1, ht, hb, recvs, sends = pkg.halo_plan(h, world, rank, spread)
+              buf = full[r0 - ht:r1 + hb].contiguous()
+              out = torch.empty((r1 - r0, w), dtype=torch.uint8, device="cuda")
+              pkg.envelope_device(buf, w, buf.shape[0], ht, ht + r1 - r0, spread, False, out)
+              torch.cuda.synchronize()
+              assert np.array_equal(out.cpu().numpy(), want[r0:r1]), (world, rank)
 
 
 @pytest.mark.parametrize("n,spread", [(4096, 64)])

@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol(pkg):
     L = pkg.lib()
     for s in declared:
         assert hasattr(L, s), s
-    assert L.chaqsdf_version() == 100
+    assert L.chaqsdf_version() == 110
 
 
 def test_no_gpu_means_error_not_fallback(pkg):
