@@ -208,76 +208,28 @@ int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, 
     return CHAQSDF_OK;
 }
 
-struct SweepGeom {
-    int wpc = 0;         // warps per CTA
-    int ctas_per_sm = 0;
-};
-std::map<std::pair<int, int>, SweepGeom> g_sweep_geom;  // (device, ring blocks) -> best CTA shape
+// CTAs of the banded pass 2 that one SM holds, per (device, ring blocks, mode); also raises the kernel's
+// opt-in shared-memory limit (sticky per kernel, so it is only ever raised).
+std::map<std::tuple<int, int, int>, int> g_sweep_ctas;
+size_t g_sweep_smem_limit[2][64] = {{0}, {0}};
 
-std::map<std::pair<int, int>, size_t> g_sweep_smem_limit;  // (device, wpc) -> opt-in limit set so far (g_mu held)
-
-// The opt-in shared-memory limit is per kernel instance and sticky: only ever raise it.
-template <int WPC>
-int sweep_raise_limit(int dev, size_t smem) {
-    size_t& cur = g_sweep_smem_limit[std::make_pair(dev, WPC)];
-    if (smem > cur) {
-        CQ_CUDA(cudaFuncSetAttribute(sweep_kernel<WPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        cur = smem;
-    }
-    return CHAQSDF_OK;
-}
-int sweep_raise_limit_any(int wpc, int dev, size_t smem) {
-    switch (wpc) {
-        case 1: return sweep_raise_limit<1>(dev, smem);
-        case 2: return sweep_raise_limit<2>(dev, smem);
-        case 4: return sweep_raise_limit<4>(dev, smem);
-        case 5: return sweep_raise_limit<5>(dev, smem);
-        case 8: return sweep_raise_limit<8>(dev, smem);
-        default: return sweep_raise_limit<10>(dev, smem);
-    }
-}
-template <int WPC>
-int sweep_occupancy(int dev, size_t smem, int* ctas) {
-    if (int rc = sweep_raise_limit<WPC>(dev, smem)) return rc;
-    CQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas, sweep_kernel<WPC>, WPC * 32, smem));
-    return CHAQSDF_OK;
-}
-
-int sweep_geometry(int nb, SweepGeom* out) {
-    DevInfo di;
-    if (int rc = device_info(&di)) return rc;
+template <bool GMODE>
+int sweep_ctas_per_sm(int nb, int* out) {
     int dev = 0;
     CQ_CUDA(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(g_mu);
-    auto key = std::make_pair(dev, nb);
-    auto it = g_sweep_geom.find(key);
-    if (it == g_sweep_geom.end()) {
-        const size_t per_warp = (size_t)nb * 1280;
-        SweepGeom best;
-        int best_warps = 0;
-        const int cand[6] = {1, 2, 4, 5, 8, 10};
-        for (int i = 0; i < 6; ++i) {
-            const int wpc = cand[i];
-            const size_t smem = per_warp * wpc;
-            if (smem > (size_t)di.max_smem_optin) continue;
-            int ctas = 0, rc = 0;
-            switch (wpc) {
-                case 1: rc = sweep_occupancy<1>(dev, smem, &ctas); break;
-                case 2: rc = sweep_occupancy<2>(dev, smem, &ctas); break;
-                case 4: rc = sweep_occupancy<4>(dev, smem, &ctas); break;
-                case 5: rc = sweep_occupancy<5>(dev, smem, &ctas); break;
-                case 8: rc = sweep_occupancy<8>(dev, smem, &ctas); break;
-                default: rc = sweep_occupancy<10>(dev, smem, &ctas); break;
-            }
-            if (rc) return rc;
-            if (ctas * wpc > best_warps) { best_warps = ctas * wpc; best.wpc = wpc; best.ctas_per_sm = ctas; }
-        }
-        if (const char* e = getenv("CHAQSDF_SWEEP_WPC")) {  // tuning override: "wpc,ctas"
-            int a = 0, b = 0;
-            if (sscanf(e, "%d,%d", &a, &b) == 2 && a > 0 && b > 0) { best.wpc = a; best.ctas_per_sm = b; best_warps = a * b; }
-        }
-        if (best_warps == 0) return fail(CHAQSDF_ERR_CUDA, "banded pass 2 does not fit in shared memory");
-        it = g_sweep_geom.emplace(key, best).first;
+    const size_t smem = sweep_smem_bytes(nb, GMODE);
+    if (dev < 64 && smem > g_sweep_smem_limit[GMODE][dev]) {
+        CQ_CUDA(cudaFuncSetAttribute(sweep_kernel<GMODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        g_sweep_smem_limit[GMODE][dev] = smem;
+    }
+    auto key = std::make_tuple(dev, nb, GMODE ? 1 : 0);
+    auto it = g_sweep_ctas.find(key);
+    if (it == g_sweep_ctas.end()) {
+        int ctas = 0;
+        CQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, sweep_kernel<GMODE>, kSweepWarps * 32, smem));
+        if (const char* e = getenv("CHAQSDF_SWEEP_CTAS")) ctas = atoi(e) > 0 ? atoi(e) : ctas;  // tuning override
+        it = g_sweep_ctas.emplace(key, ctas).first;
     }
     *out = it->second;
     return CHAQSDF_OK;
@@ -292,36 +244,39 @@ int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_b
     p.rs = (long long)banded_rs(w); p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
     p.out_begin = (int)out_begin; p.out_end = (int)out_end;
     p.ncg = (int)((w + 31) / 32);
+    p.nstrips = (p.ncg + kSweepWarps - 1) / kSweepWarps;
     p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2; p.nb = sweep_ring_blocks(p.L);
     const long long out_rows = (long long)(out_end - out_begin);
-    p.total_rows = (long long)n_img * p.ncg * out_rows;
-    SweepGeom g;
-    if (int rc = sweep_geometry(p.nb, &g)) return rc;
-    const long long slots = (long long)di.sms * g.ctas_per_sm * g.wpc;
+    p.total_rows = (long long)n_img * p.nstrips * out_rows;
+    // keep the whole window in shared memory when that still leaves enough warps to hide latency; otherwise
+    // stage only the push side and re-read older rows through L1/L2
+    int ctas_s = 0, ctas_g = 0;
+    bool gmode = false;
+    if (sweep_smem_bytes(p.nb, false) <= (size_t)di.max_smem_optin) {
+        if (int rc = sweep_ctas_per_sm<false>(p.nb, &ctas_s)) return rc;
+    }
+    if (ctas_s * kSweepWarps < 24) {
+        if (int rc = sweep_ctas_per_sm<true>(p.nb, &ctas_g)) return rc;
+        gmode = ctas_g > ctas_s;
+    }
+    if (const char* e = getenv("CHAQSDF_SWEEP_MODE")) {
+        if (e[0] == 'G') { if (int rc = sweep_ctas_per_sm<true>(p.nb, &ctas_g)) return rc; gmode = true; }
+        else if (e[0] == 'S' && ctas_s > 0) gmode = false;
+    }
+    const int ctas = gmode ? ctas_g : ctas_s;
+    if (ctas < 1) return fail(CHAQSDF_ERR_CUDA, "banded pass 2 does not fit in shared memory");
+    const long long slots = (long long)di.sms * ctas;
     long long run = (p.total_rows + slots - 1) / slots;
     long long min_run = 4LL * p.L > 128 ? 4LL * p.L : 128;  // keep the 2L rows of re-read context under ~50 %
     if (min_run > out_rows) min_run = out_rows;
     if (run < min_run) run = min_run;
     if (const char* e = getenv("CHAQSDF_BAND_ROWS")) run = atoll(e) > 0 ? atoll(e) : run;
-    p.rows_per_warp = run;
-    const long long nwarps = (p.total_rows + run - 1) / run;
-    const unsigned grid = (unsigned)((nwarps + g.wpc - 1) / g.wpc);
-    const size_t smem = (size_t)p.nb * 1280 * g.wpc;
-    {
-        int dev = 0;
-        CQ_CUDA(cudaGetDevice(&dev));
-        std::lock_guard<std::mutex> lk(g_mu);
-        if (int rc = sweep_raise_limit_any(g.wpc, dev, smem)) return rc;
-    }
-    switch (g.wpc) {
-        case 1: sweep_kernel<1><<<grid, 32, smem, st>>>(p); break;
-        case 2: sweep_kernel<2><<<grid, 64, smem, st>>>(p); break;
-        case 4: sweep_kernel<4><<<grid, 128, smem, st>>>(p); break;
-        case 5: sweep_kernel<5><<<grid, 160, smem, st>>>(p); break;
-        case 8: sweep_kernel<8><<<grid, 256, smem, st>>>(p); break;
-        default: sweep_kernel<10><<<grid, 320, smem, st>>>(p); break;
-    }
-    CQ_LAUNCHED("sweep_kernel<" + std::to_string(g.wpc) + ">", grid, smem);
+    p.rows_per_cta = run;
+    const unsigned grid = (unsigned)((p.total_rows + run - 1) / run);
+    const size_t smem = sweep_smem_bytes(p.nb, gmode);
+    if (gmode) sweep_kernel<true><<<grid, kSweepWarps * 32, smem, st>>>(p);
+    else sweep_kernel<false><<<grid, kSweepWarps * 32, smem, st>>>(p);
+    CQ_LAUNCHED(gmode ? "sweep_kernel<G>" : "sweep_kernel<S>", grid, smem);
     return CHAQSDF_OK;
 }
 

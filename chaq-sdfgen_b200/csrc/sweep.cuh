@@ -13,9 +13,11 @@
 // envelope ever re-reads. Class bits arrive as one 32-bit word per row and are transposed in the warp
 // (5 shuffle stages) into one word per column. Nothing is transposed through global memory.
 //
-// Work split: the (image, column group, row) space is linearised and cut into equal runs, one per resident
-// warp, so a launch is a single wave on 148 SMs whatever the image shape; a run that crosses a column-group
-// boundary is finished as two pieces. Each piece re-reads L rows of context above and below itself.
+// Work split: a CTA of kSweepWarps warps owns a strip of 32*kSweepWarps adjacent columns, so its warps read
+// the same 128-byte lines of the record at about the same time. The (image, strip, row) space is linearised
+// and cut into equal runs, one per resident CTA, so a launch is a single wave on 148 SMs whatever the image
+// shape; a run that crosses a strip boundary is finished as two pieces. Each piece re-reads L rows of context
+// above and below itself.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -23,6 +25,8 @@
 #include "tables.h"
 
 namespace chaq {
+
+constexpr int kSweepWarps = 4;
 
 struct SweepParams {
     const uint8_t* inter;    // banded intermediate, [n_img][buf_rows] records
@@ -32,11 +36,25 @@ struct SweepParams {
     int wp;                  // padded width (bytes of g8 per record)
     int w, buf_rows;
     int out_begin, out_end;  // rows of the buffer to produce
-    int ncg;                 // column groups per image = ceil(w/32)
-    long long total_rows;    // n_img * ncg * (out_end-out_begin): the linearised work
-    long long rows_per_warp; // run length per warp
+    int ncg;                 // column groups (32 columns) per image = ceil(w/32)
+    int nstrips;             // strips per image = ceil(ncg / kSweepWarps)
+    long long total_rows;    // n_img * nstrips * (out_end-out_begin): the linearised work
+    long long rows_per_cta;  // run length per CTA
     int nb, L, c2;           // ring blocks, lag, clamp
 };
+
+constexpr int kSweepTableBytes = 2176;  // 2*260 int32 thresholds, padded to 128
+constexpr int kSweepStageBlocks = 3;    // GMODE: blocks of g8 staged in shared memory on the push side only
+// Two ways to keep the g8 rows that the envelope re-reads:
+//   GMODE = false: all 2L+64 rows of the window in the shared-memory ring (no global re-read at all);
+//   GMODE = true : only the block being pushed (and the one being prefetched) in shared memory, older rows are
+//                  re-read through L1/L2 -- 3x less shared memory per warp, so 3x more warps hide that latency.
+__host__ __device__ inline size_t sweep_warp_smem(int nb, bool gmode) {
+    return (size_t)(gmode ? kSweepStageBlocks : nb) * 1024 + (size_t)nb * 256;
+}
+__host__ __device__ inline size_t sweep_smem_bytes(int nb, bool gmode) {
+    return kSweepTableBytes + (size_t)kSweepWarps * sweep_warp_smem(nb, gmode);
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
@@ -56,26 +74,30 @@ __device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
     return x;
 }
 
+template <bool GMODE>
 struct SweepCtx {
     // this warp's rings in shared memory
-    uint8_t* gring;      // [nb][32 rows][32 lanes]
-    uint32_t* hring;     // [nb][32 lanes] + lane
+    const uint8_t* gring;  // [nb][32 rows][32 lanes], already offset by lane
+    const uint8_t* gpush;  // row 0 of the block being pushed, at this lane
+    uint32_t* hring;       // [nb][32 lanes], already offset by lane
     uint32_t* cring;
-    uint32_t gring_s;    // shared-space address of gring
+    uint32_t gring_s;      // shared-space address of the ring (lane 0)
     int nb, lane;
+    int gslot;             // GMODE: staging slot of the block being pushed
     // current piece
     const uint8_t* rec0;   // record of relative row 0, at this warp's first column (16-byte aligned)
-    const uint32_t* cls0;  // class word of relative row 0 for this column group
+    const uint8_t* cls0;   // class word of relative row 0 for this column group
     long long rs;
     int nrows;             // relative rows that exist
     int nblk;              // blocks that will be pushed
     uint32_t craw_next;    // class word of row (blk+1)*32+lane, loaded one block ahead
     uint32_t craw;
     // epilogue
-    const int32_t* thr;    // LevelTable::thr
-    uint8_t* o8;           // output of relative row 0 at this lane's column (nullptr: column outside the image)
+    const int32_t* thr;    // shared-memory copy of LevelTable::thr
+    uint8_t* optr;         // where the next result goes (nullptr: column outside the image)
     long long ostride;
     int qcls, qm, qlo, qhi;
+    const int32_t* qthr;
 
     __device__ __forceinline__ void issue(int blk, int slot) {
         if (blk < nblk) {
@@ -91,81 +113,102 @@ struct SweepCtx {
     __device__ __forceinline__ uint32_t ldg_cls(int blk) {
         int r = blk * 32 + lane;
         r = r < nrows ? r : nrows - 1;
-        return __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(cls0) + (long long)r * rs));
+        return __ldg(reinterpret_cast<const uint32_t*>(cls0 + (long long)r * rs));
     }
     __device__ __forceinline__ void block_begin(int blk, int slot) {
         __syncwarp();  // every lane is done with the block whose slot the next prefetch overwrites
+        if (GMODE) {   // own small ring: slot = blk mod kSweepStageBlocks
+            if (blk == 0) gslot = 0; else gslot = gslot + 1 == kSweepStageBlocks ? 0 : gslot + 1;
+            slot = gslot;
+        }
+        const int ring_blocks = GMODE ? kSweepStageBlocks : nb;
         if (blk == 0) {
             issue(0, slot);
             craw_next = ldg_cls(0);
         }
-        issue(blk + 1, slot + 1 == nb ? 0 : slot + 1);
+        issue(blk + 1, slot + 1 == ring_blocks ? 0 : slot + 1);
         cp_async_wait1();
         __syncwarp();
         craw = craw_next;
         craw_next = ldg_cls(blk + 1);
+        gpush = gring + slot * 1024;
     }
     __device__ __forceinline__ uint32_t cls_fetch(int) { return warp_transpose32(craw, lane); }
-    __device__ __forceinline__ uint32_t ld_g(int slot, int j) const { return gring[slot * 1024 + j * 32 + lane]; }
+    __device__ __forceinline__ uint32_t g_push(int j) const { return gpush[j * 32]; }
+    __device__ __forceinline__ uint32_t g_at(int blk, int slot, int j) const {
+        if (GMODE) return __ldg(rec0 + (long long)(blk * 32 + j) * rs + lane);
+        return gring[slot * 1024 + j * 32];
+    }
     __device__ __forceinline__ uint32_t hull_ld(int s) const { return hring[s * 32]; }
     __device__ __forceinline__ void hull_st(int s, uint32_t v) { hring[s * 32] = v; }
     __device__ __forceinline__ uint32_t cls_ld(int s) const { return cring[s * 32]; }
     __device__ __forceinline__ void cls_st(int s, uint32_t v) { cring[s * 32] = v; }
-    __device__ __forceinline__ void out(int rr, int cls, int d2c) {
+    __device__ __forceinline__ void out(int cls, int d2c) {
         if (cls != qcls) {
             qcls = cls;
-            qm = level_of(thr + cls * 260, d2c);
-            qlo = __ldg(thr + cls * 260 + qm);
-            qhi = __ldg(thr + cls * 260 + qm + 1);
+            qthr = thr + cls * 260;
+            qm = level_of(qthr, d2c);
+            qlo = qthr[qm];
+            qhi = qthr[qm + 1];
         } else {
-            while (d2c >= qhi) { ++qm; qlo = qhi; qhi = __ldg(thr + cls * 260 + qm + 1); }
-            while (d2c < qlo) { --qm; qhi = qlo; qlo = __ldg(thr + cls * 260 + qm); }
+            while (d2c >= qhi) { ++qm; qlo = qhi; qhi = qthr[qm + 1]; }
+            while (d2c < qlo) { --qm; qhi = qlo; qlo = qthr[qm]; }
         }
-        if (o8) o8[(long long)rr * ostride] = (uint8_t)(cls ? qm : 255 - qm);
+        if (optr) {
+            *optr = (uint8_t)(cls ? qm : 255 - qm);
+            optr += ostride;
+        }
     }
 };
 
-template <int WPC>
-__global__ void __launch_bounds__(WPC * 32) sweep_kernel(SweepParams p) {
+template <bool GMODE>
+__global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 6 : 2) sweep_kernel(SweepParams p) {
     extern __shared__ __align__(16) uint8_t s_sweep[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const size_t per_warp = (size_t)p.nb * (1024 + 128 + 128);
-    uint8_t* base = s_sweep + (size_t)warp * per_warp;
+    int32_t* s_thr = reinterpret_cast<int32_t*>(s_sweep);
+    for (int i = threadIdx.x; i < 2 * 260; i += kSweepWarps * 32) s_thr[i] = (&p.table->thr[0][0])[i];
+    __syncthreads();
+    uint8_t* base = s_sweep + kSweepTableBytes + (size_t)warp * sweep_warp_smem(p.nb, GMODE);
+    const int gblocks = GMODE ? kSweepStageBlocks : p.nb;
 
-    SweepCtx c;
-    c.gring = base;
-    c.hring = reinterpret_cast<uint32_t*>(base + (size_t)p.nb * 1024) + lane;
+    SweepCtx<GMODE> c;
+    c.gslot = 0;
+    c.gring = base + lane;
+    c.gpush = c.gring;
+    c.hring = reinterpret_cast<uint32_t*>(base + (size_t)gblocks * 1024) + lane;
     c.cring = c.hring + p.nb * 32;
     c.gring_s = smem_u32(base);
     c.nb = p.nb; c.lane = lane; c.rs = p.rs;
-    c.thr = &p.table->thr[0][0];
+    c.thr = s_thr;
     c.ostride = p.w;
 
     const int out_rows = p.out_end - p.out_begin;
-    const long long slot = (long long)blockIdx.x * WPC + warp;
-    long long lin = slot * p.rows_per_warp;
-    long long lin_end = lin + p.rows_per_warp;
+    long long lin = (long long)blockIdx.x * p.rows_per_cta;
+    long long lin_end = lin + p.rows_per_cta;
     if (lin_end > p.total_rows) lin_end = p.total_rows;
     while (lin < lin_end) {
-        const long long piece = lin / out_rows;         // (image, column group)
+        const long long piece = lin / out_rows;         // (image, strip)
         const int ya = (int)(lin - piece * out_rows);   // first output row (relative to out_begin)
-        long long rest = lin_end - lin;
+        const long long rest = lin_end - lin;
         const int yb = (int)(rest < (long long)(out_rows - ya) ? ya + rest : out_rows);
-        const int img = (int)(piece / p.ncg), cg = (int)(piece - (long long)img * p.ncg);
-        const int y0 = p.out_begin + ya, y1 = p.out_begin + yb;  // buffer rows
-        const int row0 = (y0 - p.L > 0 ? y0 - p.L : 0) & ~31;
-        const uint8_t* recbase = p.inter + ((long long)img * p.buf_rows + row0) * p.rs;
-        c.rec0 = recbase + cg * 32;
-        c.cls0 = reinterpret_cast<const uint32_t*>(recbase + p.wp) + cg;
-        c.nrows = p.buf_rows - row0;
-        const int tend = (c.nrows < (y1 - row0) + p.L) ? c.nrows : (y1 - row0) + p.L;
-        c.nblk = (tend + 31) >> 5;
-        const int x = cg * 32 + lane;
-        c.o8 = x < p.w ? p.out + ((long long)img * out_rows + (row0 - p.out_begin)) * (long long)p.w + x : nullptr;
-        c.qcls = -1; c.qm = 0; c.qlo = 0; c.qhi = 0;
-        ColumnSweep<SweepCtx> sw(c, p.nb, p.L, p.c2);
-        sw.run(c.nrows, y0 - row0, y1 - row0);
-        __syncwarp();
+        const int img = (int)(piece / p.nstrips), strip = (int)(piece - (long long)img * p.nstrips);
+        const int cg = strip * kSweepWarps + warp;
+        if (cg < p.ncg) {
+            const int y0 = p.out_begin + ya, y1 = p.out_begin + yb;  // buffer rows
+            const int row0 = (y0 - p.L > 0 ? y0 - p.L : 0) & ~31;
+            const uint8_t* recbase = p.inter + ((long long)img * p.buf_rows + row0) * p.rs;
+            c.rec0 = recbase + cg * 32;
+            c.cls0 = recbase + p.wp + cg * 4;
+            c.nrows = p.buf_rows - row0;
+            const int tend = (c.nrows < (y1 - row0) + p.L) ? c.nrows : (y1 - row0) + p.L;
+            c.nblk = (tend + 31) >> 5;
+            const int x = cg * 32 + lane;
+            c.optr = x < p.w ? p.out + ((long long)img * out_rows + ya) * (long long)p.w + x : nullptr;
+            c.qcls = -1; c.qm = 0; c.qlo = 0; c.qhi = 0; c.qthr = s_thr;
+            ColumnSweep<SweepCtx<GMODE>> sw(c, p.nb, p.L, p.c2);
+            sw.run(c.nrows, y0 - row0, y1 - row0);
+            __syncwarp();
+        }
         lin += yb - ya;
     }
 }

@@ -34,13 +34,15 @@ namespace chaq {
 constexpr int kFarRow = 1 << 28;  // "no such row"; survives +- image-size arithmetic without overflow
 
 // Ctx must provide (slot = ring slot of a 32-row block, j = row within the block):
-//   void     block_begin(int blk, int slot)   block `blk` is about to be pushed: its g8 rows must be readable
+//   void     block_begin(int blk, int slot)   block `blk` is about to be pushed into `slot`: its g8 rows must be
+//                                             readable from now on
 //   uint32_t cls_fetch(int blk)               class bits of this column for the 32 rows of block blk
 //                                             (rows past the end of the buffer repeat the last real row)
-//   uint32_t ld_g(int slot, int j)            g8 of a ring row
+//   uint32_t g_push(int j)                    g8 of row j of the block being pushed
+//   uint32_t g_at(int blk, int slot, int j)   g8 of row j of block blk (ring slot `slot`), blk within 2L rows
 //   uint32_t hull_ld(int slot) / void hull_st(int slot, uint32_t)
 //   uint32_t cls_ld(int slot)  / void cls_st(int slot, uint32_t)
-//   void     out(int rr, int cls, int d2c)    result for relative row rr (d2c already clamped to C^2)
+//   void     out(int cls, int d2c)            next result (rows arrive in order from y0; d2c clamped to C^2)
 template <class Ctx>
 struct ColumnSweep {
     Ctx& c;
@@ -55,6 +57,10 @@ struct ColumnSweep {
     bool einit;
     int ecls, upd, nb;      // class of the run being emitted, rows since it began (+1), first row of the next run
     int cur_p, cur_h, nxt_p, nxt_h;  // best site and its successor on the hull (-1: none)
+    // successor cursor: every hull bit after nxt_p up to the end of block eblk is in ehw, and no block between
+    // nxt's and eblk holds a hull bit. nxt_p < 0 (cur has no successor yet): eblk == pblk at that time, ehw == 0.
+    int eblk, eslot;
+    uint32_t ehw;
 
     CQ_HD ColumnSweep(Ctx& ctx, int nb_, int lag, int c2) : c(ctx), NB(nb_), L(lag), C2(c2) {}
 
@@ -65,7 +71,7 @@ struct ColumnSweep {
     CQ_HD uint32_t hull_word(int blk) { return blk == pblk ? hwp : c.hull_ld(slot_of(blk)); }
     CQ_HD uint32_t cls_word(int blk) { return blk == pblk ? cwp : c.cls_ld(slot_of(blk)); }
     CQ_HD int height_at(int rr) {
-        int g = (int)c.ld_g(slot_of(rr >> 5), rr & 31) + 1;
+        int g = (int)c.g_at(rr >> 5, slot_of(rr >> 5), rr & 31) + 1;
         return g * g;
     }
     // lowest set hull bit at a row in [from, to], or -1
@@ -124,15 +130,13 @@ struct ColumnSweep {
     }
     CQ_HD void hull_clear(int rr) {
         const uint32_t bit = 1u << (rr & 31);
-        if ((rr >> 5) == pblk) hwp &= ~bit;
+        const int b = rr >> 5;
+        if (b == pblk) hwp &= ~bit;
         else {
-            int s = slot_of(rr >> 5);
+            int s = slot_of(b);
             c.hull_st(s, c.hull_ld(s) & ~bit);
         }
-    }
-    CQ_HD static bool dominated(int pa, int ha, int pb, int hb, int pc, int hc) {
-        int u = pb - pa, w = pc - pb;
-        return w * (hb - ha) - u * (hc - hb) >= u * w * (u + w);
+        if (b == eblk) ehw &= ~bit;
     }
 
     CQ_HD void reset() {
@@ -140,6 +144,7 @@ struct ColumnSweep {
         top_p = sec_p = -1; top_h = sec_h = 0;
         einit = false; ecls = 0; upd = kFarRow; nb = kFarRow;
         cur_p = nxt_p = -1; cur_h = nxt_h = 0;
+        eblk = 0; eslot = 0; ehw = 0u;
     }
 
     // a new block of 32 rows starts: retire the previous one to the rings, fetch the class bits of the new one
@@ -160,9 +165,9 @@ struct ColumnSweep {
         }
     }
 
-    CQ_HD void push(int rr) {
+    CQ_HD void push(int rr, int j) {
         tlast = rr;
-        const int g8 = (int)c.ld_g(pslot, rr & 31);
+        const int g8 = (int)c.g_push(j);
         if (g8 >= L) return;  // no opposite pixel within reach along this row
         const int h = (g8 + 1) * (g8 + 1);
         const int lowb = rr - 2 * L;
@@ -170,46 +175,71 @@ struct ColumnSweep {
         if (top_p < lowb) { top_p = -1; sec_p = -1; }
         else if (sec_p < lowb) sec_p = -1;
         int popfloor = kFarRow;
-        while (sec_p >= 0 && dominated(sec_p, sec_h, top_p, top_h, rr, h)) {
+        while (sec_p >= 0) {
+            const int u = top_p - sec_p, w = rr - top_p;
+            if (w * (top_h - sec_h) - u * (h - top_h) < u * w * (u + w)) break;  // top stays on the hull
             hull_clear(top_p);
             popfloor = top_p;
             top_p = sec_p; top_h = sec_h;
             sec_p = hull_down(top_p - 1, cq_max(lowb, 0));
             sec_h = sec_p >= 0 ? height_at(sec_p) : 0;
         }
-        hwp |= 1u << (rr & 31);
+        const uint32_t bit = 1u << j;
+        hwp |= bit;
         sec_p = top_p; sec_h = top_h;
         top_p = rr; top_h = h;
         // emission side: every site from popfloor up to rr-1 has just left the hull
-        if (cur_p < 0 || popfloor <= cur_p) { cur_p = rr; cur_h = h; nxt_p = -1; }
-        else if (nxt_p < 0 || popfloor <= nxt_p) { nxt_p = rr; nxt_h = h; }
+        if (cur_p < 0 || popfloor <= cur_p) { cur_p = rr; cur_h = h; nxt_p = -1; eblk = pblk; eslot = pslot; ehw = 0u; }
+        else if (nxt_p < 0 || popfloor <= nxt_p) { nxt_p = rr; nxt_h = h; eblk = pblk; eslot = pslot; ehw = 0u; }
+        else if (eblk == pblk) ehw |= bit;
+    }
+
+    // nxt := the hull site after nxt (nxt_p >= 0 on entry)
+    CQ_HD void next_site() {
+        if (ehw == 0u) {
+            int b = eblk;
+            while (b < pblk) {
+                ++b;
+                const uint32_t wd = hull_word(b);
+                if (wd) { ehw = wd; eblk = b; eslot = slot_of(b); break; }
+            }
+            if (ehw == 0u) { nxt_p = -1; eblk = pblk; eslot = pslot; return; }
+        }
+        const int j = cq_lowbit(ehw);
+        ehw &= ehw - 1u;
+        nxt_p = eblk * 32 + j;
+        const int g = (int)c.g_at(eblk, eslot, j) + 1;
+        nxt_h = g * g;
     }
 
     CQ_HD void seek(int from) {  // cur := first hull site at or after `from`, nxt := its successor
-        int p = hull_up(from, tlast);
+        const int p = hull_up(from, tlast);
         cur_p = p;
         if (p >= 0) {
             cur_h = height_at(p);
-            int q = hull_up(p + 1, tlast);
-            nxt_p = q;
-            if (q >= 0) nxt_h = height_at(q);
+            eblk = p >> 5; eslot = slot_of(eblk);
+            ehw = hull_word(eblk) & ~((2u << (p & 31)) - 1u);
+            nxt_p = p;
+            next_site();
         } else {
-            nxt_p = -1;
+            nxt_p = -1; eblk = pblk; eslot = pslot; ehw = 0u;
         }
     }
 
+    CQ_HD void init_emit(int er) {
+        einit = true;
+        ecls = (int)(cls_word(er >> 5) >> (er & 31)) & 1;
+        const int a = cls_down(er - 1, 0, ecls);
+        upd = a >= 0 ? er - a - 1 : kFarRow;  // emit() adds the 1
+        const int n = cls_up(er + 1, lastknown, ecls);
+        nb = n >= 0 ? n : kFarRow;
+    }
+
     CQ_HD void emit(int er) {
-        if (!einit) {
-            einit = true;
-            ecls = (int)(cls_word(er >> 5) >> (er & 31)) & 1;
-            int a = cls_down(er - 1, 0, ecls);
-            upd = a >= 0 ? er - a : kFarRow;
-            int n = cls_up(er + 1, lastknown, ecls);
-            nb = n >= 0 ? n : kFarRow;
-        } else if (er == nb) {
+        if (er == nb) {
             ecls ^= 1;
             upd = 1;
-            int n = cls_up(er + 1, lastknown, ecls);
+            const int n = cls_up(er + 1, lastknown, ecls);
             nb = n >= 0 ? n : kFarRow;
         } else {
             ++upd;
@@ -217,38 +247,51 @@ struct ColumnSweep {
         // A site more than L rows above er no longer matters, and what follows it in the bitmask may have
         // survived only because its own predecessor had been forgotten: restart at the first site in reach.
         if (cur_p >= 0 && cur_p < er - L) seek(er - L);
-        int cand = kBig;
+        int cand = C2;
         if (cur_p >= 0) {
-            int d = er - cur_p;
+            const int d = er - cur_p;
             int fc = d * d + cur_h;
             while (nxt_p >= 0) {
-                int dn = er - nxt_p;
-                int fn = dn * dn + nxt_h;
+                const int dn = er - nxt_p;
+                const int fn = dn * dn + nxt_h;
                 if (fn > fc) break;
                 cur_p = nxt_p; cur_h = nxt_h; fc = fn;
-                int q = hull_up(cur_p + 1, tlast);
-                nxt_p = q;
-                if (q >= 0) nxt_h = height_at(q);
+                next_site();
             }
-            cand = fc;
+            cand = cq_min(cand, fc);
         }
-        int v = cq_min(cq_min(upd, nb - er), L + 1);
-        c.out(er, ecls, cq_min(cand, v * v));
+        const int v = cq_min(upd, nb - er);
+        if (v <= L) cand = cq_min(cand, v * v);
+        c.out(ecls, cand);
     }
 
-    // relative rows [0, nrows) exist; results for rows [y0, y1). Row 0 must be a multiple of 32 rows into the
-    // buffer and at most... at least L rows above y0 unless it is the top of the buffer.
+    template <bool PUSH, bool EMIT>
+    CQ_HD void rows(int base, int j0, int j1) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll 2
+#endif
+        for (int j = j0; j < j1; ++j) {
+            if (PUSH) push(base + j, j);
+            if (EMIT) emit(base + j - L);
+        }
+    }
+
+    // relative rows [0, nrows) exist; results for rows [y0, y1). Row 0 of the piece is a multiple of 32 rows
+    // into the buffer and at least L rows above y0 unless it is the top of the buffer.
     CQ_HD void run(int nrows, int y0, int y1) {
         reset();
-        const int tend = cq_min(nrows, y1 + L);
-        const int stop = y1 + L;
-        for (int rr = 0; rr < stop; ++rr) {
-            if (rr < tend) {
-                if ((rr & 31) == 0) begin_block(rr >> 5, rr == 0);
-                push(rr);
-            }
-            const int er = rr - L;
-            if (er >= y0) emit(er);
+        const int tend = cq_min(nrows, y1 + L);  // rows [0, tend) are pushed
+        const int stop = y1 + L;                 // row er = rr - L is emitted for rr in [y0 + L, stop)
+        for (int base = 0; base < stop; base += 32) {
+            if (base < tend) begin_block(base >> 5, base == 0);
+            const int jstop = cq_min(32, stop - base);
+            const int jpush = cq_max(0, cq_min(jstop, tend - base));
+            const int jemit = cq_max(0, cq_min(jstop, y0 + L - base));
+            const int lo = cq_min(jpush, jemit), hi = cq_max(jpush, jemit);
+            rows<true, false>(base, 0, lo);
+            if (!einit && jemit < jstop) init_emit(y0);
+            if (jemit < jpush) rows<true, true>(base, lo, hi);
+            rows<false, true>(base, hi, jstop);
         }
     }
 };

@@ -35,7 +35,9 @@ struct Ctx2 {
     std::vector<uint32_t> hull, cls;
     int* d2; uint8_t* ocls; int y0;
     long oob = 0;
+    int cur_slot = 0, nout = 0;
     void block_begin(int blk, int slot) {
+        cur_slot = slot;
         slot_blk[slot] = blk;
         slot_blk[(slot + 1) % NB] = blk + 1;  // the prefetch of the next block lands there now
     }
@@ -48,8 +50,10 @@ struct Ctx2 {
         }
         return wd;
     }
-    uint32_t ld_g(int slot, int j) {
+    uint32_t g_push(int j) { return g_at(slot_blk[cur_slot], cur_slot, j); }
+    uint32_t g_at(int blk, int slot, int j) {
         if (slot < 0 || slot >= NB) { ++oob; return 0; }
+        if (slot_blk[slot] != blk) ++oob;  // the ring no longer holds that block
         int r = slot_blk[slot] * 32 + j;
         if (r < 0 || r >= nrows) { ++oob; return 0; }
         return gcol[(size_t)r * stride];
@@ -58,7 +62,7 @@ struct Ctx2 {
     void hull_st(int s, uint32_t v) { if (s < 0 || s >= NB) { ++oob; return; } hull[s] = v; }
     uint32_t cls_ld(int s) { if (s < 0 || s >= NB) { ++oob; return 0; } return cls[s]; }
     void cls_st(int s, uint32_t v) { if (s < 0 || s >= NB) { ++oob; return; } cls[s] = v; }
-    void out(int rr, int c, int v) { d2[rr - y0] = v; ocls[rr - y0] = (uint8_t)c; }
+    void out(int c, int v) { d2[nout] = v; ocls[nout] = (uint8_t)c; ++nout; }
 };
 
 // mask: h*w bytes of 0/1. band_rows: split each column into bands finished independently (0 = one band).
@@ -88,6 +92,7 @@ extern "C" int emul2_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
             c.d2 = cd2.data() + y0; c.ocls = ccls.data() + y0; c.y0 = y0 - row0;
             ColumnSweep<Ctx2> sw(c, NB, L, lt.c2);
             sw.run(h - row0, y0 - row0, y1 - row0);
+            if (c.nout != y1 - y0) return 2;
             if (c.oob) return 1000 + (int)(c.oob > 1000000 ? 1000000 : c.oob);
         }
         for (int y = 0; y < h; ++y) {
