@@ -94,9 +94,10 @@ struct SweepCtx {
     uint32_t craw;
     // epilogue
     const int32_t* thr;    // shared-memory copy of LevelTable::thr
-    uint8_t* optr;         // where the next result goes (nullptr: column outside the image)
+    uint8_t* optr;         // where the next result goes
+    bool store_ok;         // false: this lane's column is outside the image
     long long ostride;
-    int qcls, qm, qlo, qhi;
+    int qcls, qm, qlo, qspan, qbyte;
     const int32_t* qthr;
 
     __device__ __forceinline__ void issue(int blk, int slot) {
@@ -143,21 +144,25 @@ struct SweepCtx {
     __device__ __forceinline__ void hull_st(int s, uint32_t v) { hring[s * 32] = v; }
     __device__ __forceinline__ uint32_t cls_ld(int s) const { return cring[s * 32]; }
     __device__ __forceinline__ void cls_st(int s, uint32_t v) { cring[s * 32] = v; }
-    __device__ __forceinline__ void out(int cls, int d2c) {
+    // the byte is a step function of d2c (tables.h); consecutive rows mostly stay on the same step, so keep the
+    // current step [qlo, qlo+qspan) and its byte, and walk the table only when d2c leaves it
+    __device__ __forceinline__ void requant(int cls, int d2c) {
         if (cls != qcls) {
             qcls = cls;
             qthr = thr + cls * 260;
             qm = level_of(qthr, d2c);
-            qlo = qthr[qm];
-            qhi = qthr[qm + 1];
         } else {
-            while (d2c >= qhi) { ++qm; qlo = qhi; qhi = qthr[qm + 1]; }
-            while (d2c < qlo) { --qm; qhi = qlo; qlo = qthr[qm]; }
+            while (d2c >= qthr[qm + 1]) ++qm;
+            while (d2c < qthr[qm]) --qm;
         }
-        if (optr) {
-            *optr = (uint8_t)(cls ? qm : 255 - qm);
-            optr += ostride;
-        }
+        qlo = qthr[qm];
+        qspan = qthr[qm + 1] - qlo;
+        qbyte = cls ? qm : 255 - qm;
+    }
+    __device__ __forceinline__ void out(int cls, int d2c) {
+        if (CQ_UNLIKELY((unsigned)(d2c - qlo) >= (unsigned)qspan || cls != qcls)) requant(cls, d2c);
+        if (store_ok) *optr = (uint8_t)qbyte;
+        optr += ostride;
     }
 };
 
@@ -203,9 +208,12 @@ __global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 6 : 2) sweep_kernel(
             const int tend = (c.nrows < (y1 - row0) + p.L) ? c.nrows : (y1 - row0) + p.L;
             c.nblk = (tend + 31) >> 5;
             const int x = cg * 32 + lane;
-            c.optr = x < p.w ? p.out + ((long long)img * out_rows + ya) * (long long)p.w + x : nullptr;
-            c.qcls = -1; c.qm = 0; c.qlo = 0; c.qhi = 0; c.qthr = s_thr;
-            ColumnSweep<SweepCtx<GMODE>> sw(c, p.nb, p.L, p.c2);
+            c.store_ok = x < p.w;
+            c.optr = p.out + ((long long)img * out_rows + ya) * (long long)p.w + (x < p.w ? x : 0);
+            c.qcls = -1; c.qm = 0; c.qlo = 0; c.qspan = 0; c.qbyte = 0; c.qthr = s_thr;
+            int lag = p.L;
+            asm volatile("" : "+r"(lag));  // keep it in a register: it is used several times per row
+            ColumnSweep<SweepCtx<GMODE>> sw(c, p.nb, lag, p.c2);
             sw.run(c.nrows, y0 - row0, y1 - row0);
             __syncwarp();
         }

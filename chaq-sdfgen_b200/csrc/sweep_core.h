@@ -32,6 +32,14 @@
 namespace chaq {
 
 constexpr int kFarRow = 1 << 28;  // "no such row"; survives +- image-size arithmetic without overflow
+constexpr int kNoCurH = 1 << 28;  // height of the absent current site: every value it yields is >= C^2
+constexpr int kNoNxtH = 1 << 29;  // height of the absent successor: never better than any current site
+
+#if defined(__CUDA_ARCH__)
+#define CQ_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#else
+#define CQ_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#endif
 
 // Ctx must provide (slot = ring slot of a 32-row block, j = row within the block):
 //   void     block_begin(int blk, int slot)   block `blk` is about to be pushed into `slot`: its g8 rows must be
@@ -50,17 +58,19 @@ struct ColumnSweep {
     // push side
     int pblk, pslot;        // block being pushed and its ring slot
     uint32_t hwp, cwp;      // hull / class word of that block (registers until the block is complete)
-    int tlast;              // newest pushed row (relative), -1 before the first
+    int lowb;               // sites above this row are forgotten (checked once per block): pblk*32 - 2L
     int lastknown;          // last row whose class bit is known (end of the push block)
-    int top_p, top_h, sec_p, sec_h;
+    int top_p, top_h, sec_p, sec_h;  // the two newest hull sites (-1: none)
     // emission side
     bool einit;
-    int ecls, upd, nb;      // class of the run being emitted, rows since it began (+1), first row of the next run
-    int cur_p, cur_h, nxt_p, nxt_h;  // best site and its successor on the hull (-1: none)
-    // successor cursor: every hull bit after nxt_p up to the end of block eblk is in ehw, and no block between
-    // nxt's and eblk holds a hull bit. nxt_p < 0 (cur has no successor yet): eblk == pblk at that time, ehw == 0.
+    int ecls, upd, nb;      // class of the run being emitted, rows since it began, first row of the next run
+    int cur_p, cur_h;       // best site so far (none: -1, kNoCurH)
+    int nxt_p, nxt_h;       // its successor on the hull (none: -1, kNoNxtH)
+    // successor cursor: the hull sites after nxt are the set bits of (hull word of block eblk) & emask, then of
+    // the blocks after eblk; no block between nxt's and eblk holds a hull bit. ehw caches that word while
+    // eblk < pblk (for eblk == pblk the live register hwp is used).
     int eblk, eslot;
-    uint32_t ehw;
+    uint32_t ehw, emask;
 
     CQ_HD ColumnSweep(Ctx& ctx, int nb_, int lag, int c2) : c(ctx), NB(nb_), L(lag), C2(c2) {}
 
@@ -74,15 +84,13 @@ struct ColumnSweep {
         int g = (int)c.g_at(rr >> 5, slot_of(rr >> 5), rr & 31) + 1;
         return g * g;
     }
-    // lowest set hull bit at a row in [from, to], or -1
-    CQ_HD int hull_up(int from, int to) {
-        if (from > to) return -1;
-        int b = from >> 5, bend = to >> 5;
+    // lowest set hull bit at a row in [from, end of the push block], or -1
+    CQ_HD int hull_up(int from) {
+        int b = from >> 5;
         uint32_t bits = hull_word(b) & (0xFFFFFFFFu << (from & 31));
         for (;;) {
-            if (b == bend) bits &= (0xFFFFFFFFu >> (31 - (to & 31)));
             if (bits) return (b << 5) + cq_lowbit(bits);
-            if (b == bend) return -1;
+            if (b == pblk) return -1;
             ++b;
             bits = hull_word(b);
         }
@@ -135,16 +143,16 @@ struct ColumnSweep {
         else {
             int s = slot_of(b);
             c.hull_st(s, c.hull_ld(s) & ~bit);
+            if (b == eblk) ehw &= ~bit;
         }
-        if (b == eblk) ehw &= ~bit;
     }
 
     CQ_HD void reset() {
-        pblk = 0; pslot = 0; hwp = 0u; cwp = 0u; tlast = -1; lastknown = -1;
+        pblk = 0; pslot = 0; hwp = 0u; cwp = 0u; lowb = -2 * L; lastknown = -1;
         top_p = sec_p = -1; top_h = sec_h = 0;
         einit = false; ecls = 0; upd = kFarRow; nb = kFarRow;
-        cur_p = nxt_p = -1; cur_h = nxt_h = 0;
-        eblk = 0; eslot = 0; ehw = 0u;
+        cur_p = -1; cur_h = kNoCurH; nxt_p = -1; nxt_h = kNoNxtH;
+        eblk = 0; eslot = 0; ehw = 0u; emask = 0xFFFFFFFFu;
     }
 
     // a new block of 32 rows starts: retire the previous one to the rings, fetch the class bits of the new one
@@ -152,6 +160,7 @@ struct ColumnSweep {
         if (!first) {
             c.hull_st(pslot, hwp);
             c.cls_st(pslot, cwp);
+            if (eblk == pblk) ehw = hwp;  // the cursor's block is no longer live: cache its word
             pslot = (pslot + 1 == NB) ? 0 : pslot + 1;
         }
         pblk = blk;
@@ -159,70 +168,90 @@ struct ColumnSweep {
         c.block_begin(blk, pslot);
         cwp = c.cls_fetch(blk);
         lastknown = blk * 32 + 31;
+        // sites more than 2L rows above this block are out of the rings and out of reach of every row still to
+        // be finished: forget them
+        lowb = blk * 32 - 2 * L;
+        if (top_p < lowb) { top_p = -1; sec_p = -1; }
+        else if (sec_p < lowb) sec_p = -1;
         if (einit && nb == kFarRow) {  // the run being emitted was open-ended: does it end in this block?
             const uint32_t x = cwp ^ (ecls ? 0xFFFFFFFFu : 0u);
             if (x) nb = blk * 32 + cq_lowbit(x);
         }
     }
 
-    CQ_HD void push(int rr, int j) {
-        tlast = rr;
-        const int g8 = (int)c.g_push(j);
-        if (g8 >= L) return;  // no opposite pixel within reach along this row
-        const int h = (g8 + 1) * (g8 + 1);
-        const int lowb = rr - 2 * L;
-        // sites more than 2L rows back are out of the rings and out of reach of every row still to be finished
-        if (top_p < lowb) { top_p = -1; sec_p = -1; }
-        else if (sec_p < lowb) sec_p = -1;
-        int popfloor = kFarRow;
-        while (sec_p >= 0) {
-            const int u = top_p - sec_p, w = rr - top_p;
-            if (w * (top_h - sec_h) - u * (h - top_h) < u * w * (u + w)) break;  // top stays on the hull
+    // the top site is dominated by (sec, new site at rr with height h): pop until it is not. Returns the lowest
+    // popped row.
+    CQ_HD int pop_sites(int rr, int h) {
+        int popfloor;
+        for (;;) {
             hull_clear(top_p);
             popfloor = top_p;
             top_p = sec_p; top_h = sec_h;
             sec_p = hull_down(top_p - 1, cq_max(lowb, 0));
-            sec_h = sec_p >= 0 ? height_at(sec_p) : 0;
+            if (sec_p < 0) break;
+            sec_h = height_at(sec_p);
+            const int u = top_p - sec_p, w = rr - top_p;
+            if (w * (top_h - sec_h) - u * (h - top_h) < u * w * (u + w)) break;
         }
-        const uint32_t bit = 1u << j;
-        hwp |= bit;
-        sec_p = top_p; sec_h = top_h;
-        top_p = rr; top_h = h;
-        // emission side: every site from popfloor up to rr-1 has just left the hull
-        if (cur_p < 0 || popfloor <= cur_p) { cur_p = rr; cur_h = h; nxt_p = -1; eblk = pblk; eslot = pslot; ehw = 0u; }
-        else if (nxt_p < 0 || popfloor <= nxt_p) { nxt_p = rr; nxt_h = h; eblk = pblk; eslot = pslot; ehw = 0u; }
-        else if (eblk == pblk) ehw |= bit;
+        return popfloor;
     }
 
-    // nxt := the hull site after nxt (nxt_p >= 0 on entry)
-    CQ_HD void next_site() {
-        if (ehw == 0u) {
-            int b = eblk;
-            while (b < pblk) {
-                ++b;
-                const uint32_t wd = hull_word(b);
-                if (wd) { ehw = wd; eblk = b; eslot = slot_of(b); break; }
+    CQ_HD void push(int rr, int j) {
+        const int g8 = (int)c.g_push(j);
+        if (g8 < L) {  // else: no opposite pixel within reach along this row
+            const int h = (g8 + 1) * (g8 + 1);
+            int popfloor = kFarRow;
+            if (sec_p >= 0) {
+                const int u = top_p - sec_p, w = rr - top_p;
+                if (CQ_UNLIKELY(w * (top_h - sec_h) - u * (h - top_h) >= u * w * (u + w))) popfloor = pop_sites(rr, h);
             }
-            if (ehw == 0u) { nxt_p = -1; eblk = pblk; eslot = pslot; return; }
+            hwp |= 1u << j;
+            sec_p = top_p; sec_h = top_h;
+            top_p = rr; top_h = h;
+            // emission side: every site from popfloor up to rr-1 has just left the hull (unsigned: -1 = none)
+            if ((unsigned)popfloor <= (unsigned)cur_p) {
+                cur_p = rr; cur_h = h; nxt_p = -1; nxt_h = kNoNxtH;
+                eblk = pblk; eslot = pslot; emask = 0xFFFFFFFEu << j;
+            } else if ((unsigned)popfloor <= (unsigned)nxt_p) {
+                nxt_p = rr; nxt_h = h;
+                eblk = pblk; eslot = pslot; emask = 0xFFFFFFFEu << j;
+            }
         }
-        const int j = cq_lowbit(ehw);
-        ehw &= ehw - 1u;
-        nxt_p = eblk * 32 + j;
-        const int g = (int)c.g_at(eblk, eslot, j) + 1;
-        nxt_h = g * g;
+    }
+
+    // nxt := the hull site after nxt
+    CQ_HD void next_site() {
+        for (;;) {
+            const uint32_t wd = (eblk == pblk ? hwp : ehw) & emask;
+            if (wd) {
+                const int j = cq_lowbit(wd);
+                emask = 0xFFFFFFFEu << j;
+                nxt_p = eblk * 32 + j;
+                const int g = (int)c.g_at(eblk, eslot, j) + 1;
+                nxt_h = g * g;
+                return;
+            }
+            if (eblk == pblk) { nxt_p = -1; nxt_h = kNoNxtH; return; }  // later pushes into this block stay visible
+            ++eblk;
+            eslot = (eslot + 1 == NB) ? 0 : eslot + 1;
+            emask = 0xFFFFFFFFu;
+            if (eblk != pblk) ehw = c.hull_ld(eslot);
+        }
     }
 
     CQ_HD void seek(int from) {  // cur := first hull site at or after `from`, nxt := its successor
-        const int p = hull_up(from, tlast);
+        const int p = hull_up(from);
         cur_p = p;
         if (p >= 0) {
             cur_h = height_at(p);
             eblk = p >> 5; eslot = slot_of(eblk);
-            ehw = hull_word(eblk) & ~((2u << (p & 31)) - 1u);
-            nxt_p = p;
+            emask = 0xFFFFFFFEu << (p & 31);
+            if (eblk != pblk) ehw = c.hull_ld(eslot);
             next_site();
         } else {
-            nxt_p = -1; eblk = pblk; eslot = pslot; ehw = 0u;
+            cur_h = kNoCurH;
+            nxt_p = -1; nxt_h = kNoNxtH;
+            eblk = pblk; eslot = pslot; emask = 0xFFFFFFFFu;
         }
     }
 
@@ -235,41 +264,42 @@ struct ColumnSweep {
         nb = n >= 0 ? n : kFarRow;
     }
 
+    CQ_HD void class_flip(int er) {
+        ecls ^= 1;
+        upd = 1;
+        const int n = cls_up(er + 1, lastknown, ecls);
+        nb = n >= 0 ? n : kFarRow;
+    }
+
+    CQ_HD int advance(int er, int fn) {
+        int fc;
+        do {
+            cur_p = nxt_p; cur_h = nxt_h; fc = fn;
+            next_site();
+            const int dn = er - nxt_p;
+            fn = dn * dn + nxt_h;
+        } while (fn <= fc);
+        return fc;
+    }
+
     CQ_HD void emit(int er) {
-        if (er == nb) {
-            ecls ^= 1;
-            upd = 1;
-            const int n = cls_up(er + 1, lastknown, ecls);
-            nb = n >= 0 ? n : kFarRow;
-        } else {
-            ++upd;
-        }
+        ++upd;
+        if (CQ_UNLIKELY(er == nb)) class_flip(er);
         // A site more than L rows above er no longer matters, and what follows it in the bitmask may have
         // survived only because its own predecessor had been forgotten: restart at the first site in reach.
-        if (cur_p >= 0 && cur_p < er - L) seek(er - L);
-        int cand = C2;
-        if (cur_p >= 0) {
-            const int d = er - cur_p;
-            int fc = d * d + cur_h;
-            while (nxt_p >= 0) {
-                const int dn = er - nxt_p;
-                const int fn = dn * dn + nxt_h;
-                if (fn > fc) break;
-                cur_p = nxt_p; cur_h = nxt_h; fc = fn;
-                next_site();
-            }
-            cand = cq_min(cand, fc);
-        }
-        const int v = cq_min(upd, nb - er);
-        if (v <= L) cand = cq_min(cand, v * v);
-        c.out(ecls, cand);
+        const int lowrow = cq_max(er - L, 0);
+        if (CQ_UNLIKELY((unsigned)cur_p < (unsigned)lowrow)) seek(lowrow);
+        const int d = er - cur_p;
+        int fc = d * d + cur_h;
+        const int dn = er - nxt_p;
+        const int fn = dn * dn + nxt_h;
+        if (fn <= fc) fc = advance(er, fn);
+        const int v = cq_min(cq_min(upd, nb - er), L + 1);  // (L+1)^2 = C^2: the clamp comes for free
+        c.out(ecls, cq_min(fc, v * v));
     }
 
     template <bool PUSH, bool EMIT>
     CQ_HD void rows(int base, int j0, int j1) {
-#if defined(__CUDA_ARCH__)
-#pragma unroll 2
-#endif
         for (int j = j0; j < j1; ++j) {
             if (PUSH) push(base + j, j);
             if (EMIT) emit(base + j - L);
@@ -296,7 +326,7 @@ struct ColumnSweep {
     }
 };
 
-// ring blocks needed: rows [t-2L, t] stay addressable while the next block (32 rows) is being prefetched
+// ring blocks needed: rows [t-2L-31, t] stay addressable while the next block (32 rows) is being prefetched
 CQ_HD int sweep_ring_blocks(int L) { return (2 * L + 64 + 31) / 32; }
 
 }  // namespace chaq
