@@ -25,9 +25,12 @@ sys.path.insert(0, ROOT)
 
 SIDE = int(os.environ.get("CHAQ_BENCH_SIDE", 16384))
 SPREAD = int(os.environ.get("CHAQ_BENCH_SPREAD", 256))
+# dram__bytes_read+write of one pass-2 launch from the committed ncu --set full capture (profiles/), or None
+TRAFFIC_PASS2 = None
 WORKLOAD = f"config4: SYN-DISCS({SIDE}) {SIDE}x{SIDE} u8 mask, spread {SPREAD}, symmetric"
-# algorithmic bytes per pixel: pass 1 reads 1 B, writes 2 B; pass 2 reads 2 B, writes 1 B
-BYTES_PASS1, BYTES_PASS2 = 3, 3
+# algorithmic bytes: pass 1 reads the 1 B/px mask and writes the intermediate; pass 2 reads the
+# intermediate and writes the 1 B/px bitmap. The intermediate is 1 B/px of row distance + 1 bit/px of class
+# (spread <= 256), i.e. 2.125 B/px per pass at 16384^2; chaqsdf_inter_row_bytes gives the exact row size.
 
 
 def syn_discs(n, seed=88172645463325252, n_discs=200):
@@ -253,13 +256,14 @@ def run_ours(args, rank, world, local_rank):
     if world == 1:
         p1 = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
         p2 = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
-        a2 = BYTES_PASS2 * h * w / (p2 * 1e-3) / 1e9
-        a1 = BYTES_PASS1 * h * w / (p1 * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": "envelope_kernel (pass 2)", "achieved": a2, "peak": peak, "unit": "GB/s",
-                    "frac": a2 / peak, "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": BYTES_PASS2 * h * w, "ms_per_launch": p2}
-        passes = {"rowscan_kernel": {"ms": p1, "GB/s": a1, "frac": a1 / peak},
-                  "envelope_kernel": {"ms": p2, "GB/s": a2, "frac": a2 / peak}}
+        pass_bytes = h * w + h * pkg.inter_row_bytes(w, SPREAD)  # the same for both passes
+        a2 = pass_bytes / (p2 * 1e-3) / 1e9
+        a1 = pass_bytes / (p1 * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": "sweep_kernel (pass 2: column envelope + epilogue)", "achieved": a2,
+                    "peak": peak, "unit": "GB/s", "frac": a2 / peak, "traffic": TRAFFIC_PASS2, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": pass_bytes, "ms_per_launch": p2}
+        passes = {"rowscan8_kernel": {"ms": p1, "GB/s": a1, "frac": a1 / peak, "algorithmic_bytes": pass_bytes},
+                  "sweep_kernel": {"ms": p2, "GB/s": a2, "frac": a2 / peak, "algorithmic_bytes": pass_bytes}}
     # CPU baseline: the reference's own code on this box's host cores, one bounded sample
     cpu = None
     try:
@@ -279,7 +283,8 @@ def run_ours(args, rank, world, local_rank):
             "dtype": "int32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "sharding": f"row bands x{world}" + (", halo exchange of the 16-bit "
                        "intermediate (NCCL p2p)" if world > 1 else ""),
-                       "l2": "inputs larger than L2 (268 MB mask + 537 MB intermediate per step vs 126 MB L2)"},
+                       "l2": "inputs larger than L2 (268 MB mask + 302 MB intermediate + 268 MB bitmap per step vs "
+                             "126 MB L2)"},
             "roofline": roofline, "passes": passes, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks}
     print(json.dumps(line), flush=True)

@@ -1,0 +1,169 @@
+// chaq_sdfgen -- host program with the command line of the reference's OpenMP tool (reference
+// openmp/sdfgen.c:32-49 usage, :139-244 argument handling, :250-258 load, :305-347 store), running the signed
+// distance field on a B200 through the C ABI of include/chaqsdf.h (chaqsdf_u8 replaces sdfgen.c:261-300).
+//
+// Kept from the reference, because scripts depend on it:
+//   * options are recognised by the character after '-' only; "-i -" / "-o -" mean stdin / stdout;
+//   * -i -o -s -q -f take the next argument; any other "-xyz" is a bundle of flags out of h, n, l, a, and
+//     unknown letters are ignored;  -h prints the usage and exits 0;
+//   * spread 0, quality outside 1..100, or a missing -i / -o: usage on stdout, message on stderr, exit status -1;
+//   * output type: -f wins, else the three characters after the last '.' of the output name compared to
+//     png bmp jpg tga, else PNG;  the result is a 1-channel 8-bit image;
+//   * the image is decoded to (luminance, alpha) pairs; the alpha channel is tested unless -l is given.
+// Added: -t prints the time spent in the library call to stderr (the reference ignores unknown flags).
+//
+// Image decoding/encoding is stb_image / stb_image_write, compiled from the reference's include directory
+// (they are its third-party submodule; nothing is copied into this repository).
+#include <chrono>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#define STB_IMAGE_IMPLEMENTATION
+#define STB_IMAGE_WRITE_IMPLEMENTATION
+#include "stb/stb_image.h"
+#include "stb/stb_image_write.h"
+
+#include "chaqsdf.h"
+
+namespace {
+
+enum class Kind { Unknown, Png, Bmp, Jpg, Tga };
+
+struct Options {
+    const char* in = nullptr;
+    const char* out = nullptr;
+    size_t spread = 64, quality = 100;
+    size_t channel = 1;  // 1 = alpha, 0 = luminance
+    bool above = true, asymmetric = false, timing = false;
+    bool from_stdin = false, to_stdout = false;
+    Kind kind = Kind::Unknown;
+};
+
+void print_usage() {
+    std::puts("usage: chaq_sdfgen [-f filetype] -i file -o file [-q n] [-s n] [-ahln]\n"
+              "    -f filetype   output type: png, bmp, jpg or tga (default: from the output name, else png)\n"
+              "    -i file       input image; \"-\" reads stdin\n"
+              "    -o file       output image; \"-\" writes stdout\n"
+              "    -q n          jpeg quality, 1-100 (default 100)\n"
+              "    -s n          spread radius in pixels (default 64)\n"
+              "    -a            asymmetric spread: negative distances are dropped (default symmetric)\n"
+              "    -h            this text\n"
+              "    -l            test the luminance instead of the alpha channel\n"
+              "    -n            inverted test: values below the threshold are inside\n"
+              "    -t            print the time of the distance-field call to stderr");
+}
+
+[[noreturn]] void die(bool with_usage, const char* fmt, ...) {
+    if (with_usage) print_usage();
+    va_list ap;
+    va_start(ap, fmt);
+    std::vfprintf(stderr, fmt, ap);
+    va_end(ap);
+    std::fputc('\n', stderr);
+    std::exit(-1);
+}
+
+Kind kind_of(const char* s) {
+    static const struct { const char* tag; Kind k; } table[] = {{"png", Kind::Png}, {"bmp", Kind::Bmp}, {"jpg", Kind::Jpg}, {"tga", Kind::Tga}};
+    for (const auto& e : table)
+        if (std::strncmp(s, e.tag, 3) == 0) return e.k;
+    return Kind::Unknown;
+}
+
+// returns false when -h asked for the usage (exit 0)
+bool parse(int argc, char** argv, Options* o) {
+    for (int i = 0; i < argc; ++i) {
+        const char* a = argv[i];
+        if (a[0] != '-') continue;
+        const char key = a[1];
+        const bool takes_value = key == 'i' || key == 'o' || key == 's' || key == 'q' || key == 'f';
+        if (takes_value) {
+            const char* val = (i + 1 < argc) ? argv[++i] : nullptr;
+            switch (key) {
+                case 'i':
+                    if (!val) { if (!o->in) die(true, "No input file specified."); break; }
+                    o->from_stdin = std::strcmp(val, "-") == 0;
+                    o->in = val;
+                    break;
+                case 'o':
+                    if (!val) { if (!o->out) die(true, "No output file specified."); break; }
+                    o->to_stdout = std::strcmp(val, "-") == 0;
+                    o->out = val;
+                    break;
+                case 's':
+                    if (!val) die(true, "No number specified with spread.");
+                    o->spread = std::strtoull(val, nullptr, 10);
+                    break;
+                case 'q':
+                    if (!val) die(true, "No number specified with quality.");
+                    o->quality = std::strtoull(val, nullptr, 10);
+                    break;
+                default:  // 'f'
+                    if (!val) die(true, "Filetype not specified with filetype switch.");
+                    o->kind = kind_of(val);
+                    if (o->kind == Kind::Unknown) die(true, "Invalid filetype specified.");
+                    break;
+            }
+            continue;
+        }
+        for (const char* f = a + 1; *f; ++f) {
+            if (*f == 'h') { print_usage(); return false; }
+            if (*f == 'n') o->above = false;
+            else if (*f == 'l') o->channel = 0;
+            else if (*f == 'a') o->asymmetric = true;
+            else if (*f == 't') o->timing = true;
+        }
+    }
+    if (o->quality == 0 || o->quality > 100) die(true, "Invalid value given for jpeg quality. Must be between 1-100");
+    if (o->spread == 0) die(true, "Invalid value given for spread. Must be a positive integer.");
+    if (!o->in) die(true, "No input file specified.");
+    if (!o->out) die(true, "No output file specified.");
+    return true;
+}
+
+void to_stdout(void*, void* data, int size) { std::fwrite(data, (size_t)size, 1, stdout); }
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    Options o;
+    if (!parse(argc, argv, &o)) return 0;
+
+    int w = 0, h = 0, n = 0;
+    unsigned char* ya = o.from_stdin ? stbi_load_from_file(stdin, &w, &h, &n, 2) : stbi_load(o.in, &w, &h, &n, 2);
+    if (!ya) die(false, "Input file could not be opened.");
+
+    std::vector<unsigned char> sdf((size_t)w * (size_t)h);
+    const auto t0 = std::chrono::steady_clock::now();
+    const int rc = chaqsdf_u8(ya, (size_t)w, (size_t)h, 2, o.channel, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, sdf.data());
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    stbi_image_free(ya);
+    if (rc != CHAQSDF_OK) die(false, "distance field failed (%d): %s", rc, chaqsdf_last_error_string());
+    if (o.timing) std::fprintf(stderr, "chaqsdf_u8: %dx%d spread %zu in %.3f ms (%.1f Mpix/s, host buffers)\n", w, h, o.spread, ms, w * (double)h / ms / 1e3);
+
+    if (!o.to_stdout && o.kind == Kind::Unknown) {
+        if (const char* dot = std::strrchr(o.out, '.')) o.kind = kind_of(dot + 1);
+    }
+    int ok = 0;
+    switch (o.kind) {
+        case Kind::Bmp:
+            ok = o.to_stdout ? stbi_write_bmp_to_func(to_stdout, nullptr, w, h, 1, sdf.data()) : stbi_write_bmp(o.out, w, h, 1, sdf.data());
+            break;
+        case Kind::Jpg:
+            ok = o.to_stdout ? stbi_write_jpg_to_func(to_stdout, nullptr, w, h, 1, sdf.data(), (int)o.quality)
+                             : stbi_write_jpg(o.out, w, h, 1, sdf.data(), (int)o.quality);
+            break;
+        case Kind::Tga:
+            ok = o.to_stdout ? stbi_write_tga_to_func(to_stdout, nullptr, w, h, 1, sdf.data()) : stbi_write_tga(o.out, w, h, 1, sdf.data());
+            break;
+        default:
+            ok = o.to_stdout ? stbi_write_png_to_func(to_stdout, nullptr, w, h, 1, sdf.data(), w) : stbi_write_png(o.out, w, h, 1, sdf.data(), w);
+            break;
+    }
+    (void)ok;  // like the reference, a failed write is not an error status
+    return 0;
+}

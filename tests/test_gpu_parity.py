@@ -226,3 +226,40 @@ def test_error_paths(pkg):
         pkg.sdf_u8_device(d, 8, 8, spread=0)
     with pytest.raises(pkg.ChaqSdfError):
         pkg.sdf_u8_device(d, 8, 8, spread=4, workspace=torch.zeros(16, dtype=torch.uint8, device="cuda"))
+
+
+def test_cli_golden_pair_and_flags(pkg, oracle, tmp_path):
+    """The host program (reference sdfgen.c CLI contract) on the README example: -s 100 -al on the sample input
+    must give the reference's sample output, through PNG files and through stdin/stdout."""
+    import subprocess
+    from PIL import Image
+    cli = os.path.join(ROOT, "chaq-sdfgen_b200", "bin", "chaq_sdfgen")
+    if not os.path.exists(cli):
+        pytest.skip("bin/chaq_sdfgen not built")
+    z = np.load(os.path.join(GOLDEN, "sample_pair.npz"))
+    ya = z["ya"].reshape(200, 200, 2)
+    src = tmp_path / "in.png"
+    Image.fromarray(np.ascontiguousarray(ya[:, :, 0]), "L").save(src)  # 1-channel input: alpha decodes as 255
+    dst = tmp_path / "out.png"
+    r = subprocess.run([cli, "-i", str(src), "-o", str(dst), "-s", "100", "-al"], capture_output=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert np.array_equal(np.asarray(Image.open(dst)), z["out"])
+    r = subprocess.run([cli, "-i", "-", "-o", "-", "-s", "100", "-la", "-f", "bmp"], input=src.read_bytes(),
+                       capture_output=True, timeout=120)
+    assert r.returncode == 0 and r.stdout[:2] == b"BM"
+    import io
+    assert np.array_equal(np.asarray(Image.open(io.BytesIO(r.stdout)).convert("L")), z["out"])
+    # default test is the alpha channel: an image without alpha is all inside -> all 255 (SURVEY 8(c))
+    r = subprocess.run([cli, "-i", str(src), "-o", str(dst), "-s", "8"], capture_output=True, timeout=120)
+    assert r.returncode == 0 and (np.asarray(Image.open(dst)) == 255).all()
+    # -n on luminance, RGBA input with a real alpha channel
+    rng = np.random.default_rng(3)
+    rgba = rng.integers(0, 256, (90, 130, 4), dtype=np.uint8)
+    rgba[20:60, 30:100] = (250, 250, 250, 255)
+    Image.fromarray(rgba, "RGBA").save(src)
+    lum = ((77 * rgba[..., 0].astype(np.int32) + 150 * rgba[..., 1] + 29 * rgba[..., 2]) >> 8).astype(np.uint8)
+    for flags, img, above in ((["-ln"], lum, False), ([], rgba[..., 3], True), (["-a"], rgba[..., 3], True)):
+        r = subprocess.run([cli, "-i", str(src), "-o", str(dst), "-s", "12", *flags], capture_output=True, timeout=120)
+        assert r.returncode == 0, r.stderr
+        want = oracle.sdf(np.ascontiguousarray(img), 130, 90, spread=12, test_above=above, asymmetric="-a" in flags)
+        assert np.array_equal(np.asarray(Image.open(dst)), want), flags

@@ -197,3 +197,92 @@ def test_halo_exchange_gloo(tmp_path, world):
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert r.stdout.count("ok") == world
+
+
+# ---------------------------------------------------------------- banded fast path (sweep_core.h), host emulation
+@pytest.fixture(scope="session")
+def emul2(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("emul2") / "libemul2.so")
+    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-o", so,
+                    os.path.join(ROOT, "tests", "emul", "emul2.cpp")], check=True)
+    L = C.CDLL(so)
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
+    L.emul2_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, u8p, C.c_void_p, C.POINTER(C.c_int)]
+    return L
+
+
+def _emul2_u8(L, mask, spread, asym, band):
+    h, w = mask.shape
+    out = np.empty((h, w), np.uint8)
+    ce = C.c_int()
+    rc = L.emul2_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), band, out, None, C.byref(ce))
+    assert rc == 0, f"emulated banded pass failed (rc={rc}: 1 = cap_eff > 256, 2 = row count, >=1000 = stale ring access)"
+    return out, ce.value
+
+
+def test_banded_sweep_matches_oracle_random(emul2, oracle):
+    rng = np.random.default_rng(5)
+    for it in range(150):
+        h, w = int(rng.integers(1, 150)), int(rng.integers(1, 40))
+        dens = rng.choice([0.0, 0.01, 0.05, 0.3, 0.5, 0.9, 1.0])
+        mask = (rng.random((h, w)) < dens).astype(np.uint8)
+        if it % 3 == 0:
+            yy, xx = np.mgrid[0:h, 0:w]
+            mask = np.zeros((h, w), np.uint8)
+            for _ in range(3):
+                cy, cx, r = rng.integers(0, h), rng.integers(0, w), rng.integers(1, 30)
+                mask |= ((yy - cy) ** 2 + (xx - cx) ** 2 <= r * r).astype(np.uint8)
+        img = (mask * 255).astype(np.uint8)
+        for spread in (1, 2, 5, 16, 40, 100, 256):
+            for band in (0, 7, 33, 64):
+                asym = bool(it & 1)
+                got, _ = _emul2_u8(emul2, mask, spread, asym, band)
+                assert np.array_equal(got, oracle.sdf(img, w, h, spread=spread, asymmetric=asym)), (it, h, w, spread, band)
+
+
+def test_banded_sweep_discs_noise_and_cap(emul2, oracle):
+    for n, spread, band in ((384, 16, 0), (384, 64, 100), (384, 256, 0), (1024, 2, 0), (1024, 33, 300), (1024, 256, 400)):
+        img = oracle.syn_discs(n)
+        got, ce = _emul2_u8(emul2, (img > 127).astype(np.uint8), spread, False, band)
+        assert ce <= min(spread + 1, 256)
+        assert np.array_equal(got, oracle.sdf(img, n, n, spread=spread)), (n, spread, band)
+    noise = oracle.syn_noise(300)
+    got, _ = _emul2_u8(emul2, (noise > 127).astype(np.uint8), 8, True, 50)
+    assert np.array_equal(got, oracle.sdf(noise, 300, 300, spread=8, asymmetric=True))
+    # the largest spread of the banded path must still fit 8 bits, symmetric and asymmetric
+    tall = np.zeros((700, 9), np.uint8)
+    tall[300:340, 2:6] = 1
+    for asym in (False, True):
+        got, ce = _emul2_u8(emul2, tall, 256, asym, 0)
+        assert ce == 256
+        assert np.array_equal(got, oracle.sdf(tall * 255, 9, 700, spread=256, asymmetric=asym))
+
+
+# ---------------------------------------------------------------- chaq_sdfgen command line (reference sdfgen.c:122-244)
+CLI = os.path.join(ROOT, "chaq-sdfgen_b200", "bin", "chaq_sdfgen")
+
+
+def _cli(*args, stdin=None):
+    return subprocess.run([CLI, *args], input=stdin, capture_output=True, timeout=120)
+
+
+def test_cli_argument_contract(pkg):
+    if not os.path.exists(CLI):
+        pytest.skip("bin/chaq_sdfgen not built (needs the stb headers of the reference tree)")
+    r = _cli("-h")
+    assert r.returncode == 0 and r.stdout.startswith(b"usage: chaq_sdfgen [-f filetype] -i file -o file [-q n] [-s n] [-ahln]")
+    r = _cli("-alh")  # flags bundle; h anywhere in it prints the usage and exits 0 (sdfgen.c:206-209)
+    assert r.returncode == 0 and b"usage:" in r.stdout
+    for args, msg in ((("-i", "a.png", "-o", "b.png", "-s", "0"), b"Invalid value given for spread"),
+                      (("-i", "a.png", "-o", "b.png", "-q", "0"), b"Invalid value given for jpeg quality"),
+                      (("-i", "a.png", "-o", "b.png", "-q", "101"), b"Invalid value given for jpeg quality"),
+                      (("-o", "b.png"), b"No input file specified."),
+                      (("-i", "a.png"), b"No output file specified."),
+                      (("-i",), b"No input file specified."),
+                      (("-i", "a.png", "-o", "b.png", "-f", "gif"), b"Invalid filetype specified."),
+                      (("-i", "a.png", "-o", "b.png", "-s"), b"No number specified with spread.")):
+        r = _cli(*args)
+        assert r.returncode == 255, args          # exit(-1), sdfgen.c:24-30
+        assert msg in r.stderr and b"usage:" in r.stdout, args
+    r = _cli("-i", "/nonexistent/x.png", "-o", "/tmp/y.png")
+    assert r.returncode == 255 and b"Input file could not be opened." in r.stderr and b"usage:" not in r.stdout
