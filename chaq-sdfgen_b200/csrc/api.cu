@@ -266,13 +266,17 @@ int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_b
     const int ctas = gmode ? ctas_g : ctas_s;
     if (ctas < 1) return fail(CHAQSDF_ERR_CUDA, "banded pass 2 does not fit in shared memory");
     const long long slots = (long long)di.sms * ctas;
-    long long run = (p.total_rows + slots - 1) / slots;
+    int kruns = 1;  // runs per CTA (round-robin); more runs mix cheap and dear areas but re-read more context
+    if (const char* e = getenv("CHAQSDF_SWEEP_RUNS")) kruns = atoi(e) > 0 ? atoi(e) : kruns;
+    long long run = (p.total_rows + slots * kruns - 1) / (slots * kruns);
     long long min_run = 4LL * p.L > 128 ? 4LL * p.L : 128;  // keep the 2L rows of re-read context under ~50 %
     if (min_run > out_rows) min_run = out_rows;
     if (run < min_run) run = min_run;
     if (const char* e = getenv("CHAQSDF_BAND_ROWS")) run = atoll(e) > 0 ? atoll(e) : run;
     p.rows_per_cta = run;
-    const unsigned grid = (unsigned)((p.total_rows + run - 1) / run);
+    const long long nruns = (p.total_rows + run - 1) / run;
+    const unsigned grid = (unsigned)(nruns < slots ? nruns : slots);
+    p.runs_per_cta = (int)((nruns + grid - 1) / grid);
     const size_t smem = sweep_smem_bytes(p.nb, gmode);
     if (gmode) sweep_kernel<true><<<grid, kSweepWarps * 32, smem, st>>>(p);
     else sweep_kernel<false><<<grid, kSweepWarps * 32, smem, st>>>(p);

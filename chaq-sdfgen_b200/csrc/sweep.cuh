@@ -39,12 +39,13 @@ struct SweepParams {
     int ncg;                 // column groups (32 columns) per image = ceil(w/32)
     int nstrips;             // strips per image = ceil(ncg / kSweepWarps)
     long long total_rows;    // n_img * nstrips * (out_end-out_begin): the linearised work
-    long long rows_per_cta;  // run length per CTA
+    long long rows_per_cta;  // run length
+    int runs_per_cta;        // a CTA takes runs blockIdx.x, blockIdx.x + gridDim.x, ... (mixes cheap and dear areas)
     int nb, L, c2;           // ring blocks, lag, clamp
 };
 
 constexpr int kSweepTableBytes = 2176;  // 2*260 int32 thresholds, padded to 128
-constexpr int kSweepStageBlocks = 3;    // GMODE: blocks of g8 staged in shared memory on the push side only
+constexpr int kSweepStageBlocks = 2;    // GMODE: blocks of g8 staged in shared memory on the push side only
 // Two ways to keep the g8 rows that the envelope re-reads:
 //   GMODE = false: all 2L+64 rows of the window in the shared-memory ring (no global re-read at all);
 //   GMODE = true : only the block being pushed (and the one being prefetched) in shared memory, older rows are
@@ -88,6 +89,8 @@ struct SweepCtx {
     const uint8_t* rec0;   // record of relative row 0, at this warp's first column (16-byte aligned)
     const uint8_t* cls0;   // class word of relative row 0 for this column group
     long long rs;
+    const uint8_t* rec_lane;  // rec0 + lane
+    unsigned rs32;         // record stride (a piece spans < 2^31 bytes)
     int nrows;             // relative rows that exist
     int nblk;              // blocks that will be pushed
     uint32_t craw_next;    // class word of row (blk+1)*32+lane, loaded one block ahead
@@ -97,7 +100,7 @@ struct SweepCtx {
     uint8_t* optr;         // where the next result goes
     bool store_ok;         // false: this lane's column is outside the image
     long long ostride;
-    int qcls, qm, qlo, qspan, qbyte;
+    int qcls, qm, qlo, qhi, qbyte, qsign;
     const int32_t* qthr;
 
     __device__ __forceinline__ void issue(int blk, int slot) {
@@ -137,37 +140,46 @@ struct SweepCtx {
     __device__ __forceinline__ uint32_t cls_fetch(int) { return warp_transpose32(craw, lane); }
     __device__ __forceinline__ uint32_t g_push(int j) const { return gpush[j * 32]; }
     __device__ __forceinline__ uint32_t g_at(int blk, int slot, int j) const {
-        if (GMODE) return __ldg(rec0 + (long long)(blk * 32 + j) * rs + lane);
+        if (GMODE) return __ldg(rec_lane + (unsigned)(blk * 32 + j) * rs32);
         return gring[slot * 1024 + j * 32];
     }
     __device__ __forceinline__ uint32_t hull_ld(int s) const { return hring[s * 32]; }
     __device__ __forceinline__ void hull_st(int s, uint32_t v) { hring[s * 32] = v; }
     __device__ __forceinline__ uint32_t cls_ld(int s) const { return cring[s * 32]; }
     __device__ __forceinline__ void cls_st(int s, uint32_t v) { cring[s * 32] = v; }
-    // the byte is a step function of d2c (tables.h); consecutive rows mostly stay on the same step, so keep the
-    // current step [qlo, qlo+qspan) and its byte, and walk the table only when d2c leaves it
+    // the byte is a step function of d2c (tables.h); consecutive rows mostly stay on the same step or move to a
+    // neighbouring one, so keep the current step [qlo, qhi) and move one step without branching; anything
+    // else (class change, a jump of several steps) takes the slow path
     __device__ __forceinline__ void requant(int cls, int d2c) {
         if (cls != qcls) {
             qcls = cls;
             qthr = thr + cls * 260;
+            qsign = cls ? 1 : -1;
             qm = level_of(qthr, d2c);
         } else {
             while (d2c >= qthr[qm + 1]) ++qm;
             while (d2c < qthr[qm]) --qm;
         }
         qlo = qthr[qm];
-        qspan = qthr[qm + 1] - qlo;
+        qhi = qthr[qm + 1];
         qbyte = cls ? qm : 255 - qm;
     }
     __device__ __forceinline__ void out(int cls, int d2c) {
-        if (CQ_UNLIKELY((unsigned)(d2c - qlo) >= (unsigned)qspan || cls != qcls)) requant(cls, d2c);
+        const int step = (d2c >= qhi ? 1 : 0) - (d2c < qlo ? 1 : 0);
+        if (step != 0) {  // one step up or down: two table reads, no loop
+            qm += step;
+            qbyte += step * qsign;
+            qlo = qthr[qm];
+            qhi = qthr[qm + 1];
+        }
+        if (CQ_UNLIKELY(d2c >= qhi || d2c < qlo || cls != qcls)) requant(cls, d2c);
         if (store_ok) *optr = (uint8_t)qbyte;
         optr += ostride;
     }
 };
 
 template <bool GMODE>
-__global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 6 : 2) sweep_kernel(SweepParams p) {
+__global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 7 : 2) sweep_kernel(SweepParams p) {
     extern __shared__ __align__(16) uint8_t s_sweep[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int32_t* s_thr = reinterpret_cast<int32_t*>(s_sweep);
@@ -188,7 +200,8 @@ __global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 6 : 2) sweep_kernel(
     c.ostride = p.w;
 
     const int out_rows = p.out_end - p.out_begin;
-    long long lin = (long long)blockIdx.x * p.rows_per_cta;
+    for (int k = 0; k < p.runs_per_cta; ++k) {
+    long long lin = ((long long)k * gridDim.x + blockIdx.x) * p.rows_per_cta;
     long long lin_end = lin + p.rows_per_cta;
     if (lin_end > p.total_rows) lin_end = p.total_rows;
     while (lin < lin_end) {
@@ -203,6 +216,8 @@ __global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 6 : 2) sweep_kernel(
             const int row0 = (y0 - p.L > 0 ? y0 - p.L : 0) & ~31;
             const uint8_t* recbase = p.inter + ((long long)img * p.buf_rows + row0) * p.rs;
             c.rec0 = recbase + cg * 32;
+            c.rec_lane = c.rec0 + lane;
+            c.rs32 = (unsigned)p.rs;
             c.cls0 = recbase + p.wp + cg * 4;
             c.nrows = p.buf_rows - row0;
             const int tend = (c.nrows < (y1 - row0) + p.L) ? c.nrows : (y1 - row0) + p.L;
@@ -210,7 +225,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 6 : 2) sweep_kernel(
             const int x = cg * 32 + lane;
             c.store_ok = x < p.w;
             c.optr = p.out + ((long long)img * out_rows + ya) * (long long)p.w + (x < p.w ? x : 0);
-            c.qcls = -1; c.qm = 0; c.qlo = 0; c.qspan = 0; c.qbyte = 0; c.qthr = s_thr;
+            c.qcls = -1; c.qm = 1; c.qlo = 0; c.qhi = 0x7fffffff; c.qbyte = 0; c.qsign = 1; c.qthr = s_thr;
             int lag = p.L;
             asm volatile("" : "+r"(lag));  // keep it in a register: it is used several times per row
             ColumnSweep<SweepCtx<GMODE>> sw(c, p.nb, lag, p.c2);
@@ -218,6 +233,7 @@ __global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 6 : 2) sweep_kernel(
             __syncwarp();
         }
         lin += yb - ya;
+    }
     }
 }
 

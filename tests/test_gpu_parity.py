@@ -257,7 +257,8 @@ def test_cli_golden_pair_and_flags(pkg, oracle, tmp_path):
     rgba = rng.integers(0, 256, (90, 130, 4), dtype=np.uint8)
     rgba[20:60, 30:100] = (250, 250, 250, 255)
     Image.fromarray(rgba, "RGBA").save(src)
-    lum = ((77 * rgba[..., 0].astype(np.int32) + 150 * rgba[..., 1] + 29 * rgba[..., 2]) >> 8).astype(np.uint8)
+    c32 = rgba.astype(np.int32)
+    lum = ((77 * c32[..., 0] + 150 * c32[..., 1] + 29 * c32[..., 2]) >> 8).astype(np.uint8)  # stb_image.h:1726-1729
     for flags, img, above in ((["-ln"], lum, False), ([], rgba[..., 3], True), (["-a"], rgba[..., 3], True)):
         r = subprocess.run([cli, "-i", str(src), "-o", str(dst), "-s", "12", *flags], capture_output=True, timeout=120)
         assert r.returncode == 0, r.stderr
