@@ -105,6 +105,9 @@ def measured_peak():
 
 def cpu_reference_run(img, side, spread, steps, warmup):
     """The reference's own OpenMP code (oracle/_ref, compiled from the reference tree) on the host cores."""
+    if os.environ.get("OMP_NUM_THREADS") == "1" and "TORCHELASTIC_RUN_ID" in os.environ:
+        # torchrun pins OMP_NUM_THREADS=1 for its workers; the reference arm is meant to use every host thread
+        os.environ["OMP_NUM_THREADS"] = str(os.cpu_count())
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     from oracle import Ref
     r = Ref()
@@ -264,9 +267,11 @@ def run_ours(args, rank, world, local_rank):
                     "algorithmic_bytes_per_launch": pass_bytes, "ms_per_launch": p2}
         passes = {"rowscan8_kernel": {"ms": p1, "GB/s": a1, "frac": a1 / peak, "algorithmic_bytes": pass_bytes},
                   "sweep_kernel": {"ms": p2, "GB/s": a2, "frac": a2 / peak, "algorithmic_bytes": pass_bytes}}
-    # CPU baseline: the reference's own code on this box's host cores, one bounded sample
+    # CPU baseline: the reference's own code on this box's host cores, one bounded sample (N=1 only)
     cpu = None
     try:
+        if world > 1:
+            raise RuntimeError("reported at N=1 only")
         side = SIDE
         probe, threads = cpu_reference_run(img, min(4096, SIDE), SPREAD, 1, 0)
         while side > 4096 and probe[0] * (side / min(4096, SIDE)) ** 2 > 25.0:
@@ -281,8 +286,8 @@ def run_ours(args, rank, world, local_rank):
     line = {"metric": "SDF Mpix/s (inside+outside)", "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sharding": f"row bands x{world}" + (", halo exchange of the 16-bit "
-                       "intermediate (NCCL p2p)" if world > 1 else ""),
+            "config": {"workload": WORKLOAD, "sharding": f"row bands x{world}" + (", halo exchange of spread rows of the "
+                       "1.125 B/px intermediate (NCCL p2p)" if world > 1 else ""),
                        "l2": "inputs larger than L2 (268 MB mask + 302 MB intermediate + 268 MB bitmap per step vs "
                              "126 MB L2)"},
             "roofline": roofline, "passes": passes, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),

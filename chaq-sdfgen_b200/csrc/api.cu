@@ -269,7 +269,9 @@ int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_b
     int kruns = 1;  // runs per CTA (round-robin); more runs mix cheap and dear areas but re-read more context
     if (const char* e = getenv("CHAQSDF_SWEEP_RUNS")) kruns = atoi(e) > 0 ? atoi(e) : kruns;
     long long run = (p.total_rows + slots * kruns - 1) / (slots * kruns);
-    long long min_run = 4LL * p.L > 128 ? 4LL * p.L : 128;  // keep the 2L rows of re-read context under ~50 %
+    // Fill every resident CTA slot: with all slots busy the time is ~ (run + cost of 2L context rows), which only
+    // falls as runs get shorter; the floor just keeps the per-piece set-up (first block's load latency) amortised.
+    long long min_run = 64;
     if (min_run > out_rows) min_run = out_rows;
     if (run < min_run) run = min_run;
     if (const char* e = getenv("CHAQSDF_BAND_ROWS")) run = atoll(e) > 0 ? atoll(e) : run;
