@@ -17,6 +17,7 @@
 #include "rowscan.cuh"
 #include "rowscan8.cuh"
 #include "sweep.cuh"
+#include "sweep_plan.cuh"
 
 using namespace chaq;
 
@@ -110,11 +111,20 @@ int check_dims(size_t w, size_t h, size_t spread) {
 int cap_for(size_t spread) { return spread + 1 > 0x7fff ? 0x7fff : (int)(spread + 1); }
 
 // ---- intermediate formats --------------------------------------------------------------------------------
-// banded (spread <= 256): per row [Wp bytes g8 | Wp/8 bytes class bits], Wp = w rounded up to 128
+// banded (spread <= 256): per row [Wp bytes g8 | Wp/8 bytes class bits | one busy byte per 128-column strip,
+//                        padded to 16], Wp = w rounded up to 128
 // general               : per row w uint16 (bit 15 class, bits 0..14 row distance saturated at spread+1)
 bool banded(size_t spread) { return spread <= 256; }
 int banded_wp(size_t w) { return (int)align_up(w, 128); }
-size_t banded_rs(size_t w) { return (size_t)banded_wp(w) + (size_t)banded_wp(w) / 8; }
+size_t banded_rs(size_t w) {
+    const size_t wp = (size_t)banded_wp(w);
+    return wp + wp / 8 + align_up(wp / 128, 16);
+}
+// scratch of the banded pass 2's work split (sweep_plan.cuh): block-busy bytes + cut points
+size_t sweep_plan_bytes(size_t n_img, size_t w, size_t buf_rows) {
+    const size_t nstrips = (size_t)banded_wp(w) / 128, nblk = (buf_rows + 31) / 32;
+    return align_up(n_img * nstrips * nblk, 256) + align_up((size_t)(kSweepMaxCtas + 1) * sizeof(long long), 256);
+}
 size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w) : w * sizeof(uint16_t); }
 
 // launch geometry of the general pass 2
@@ -201,6 +211,7 @@ int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, 
     rp.wp = banded_wp(w); rp.w = (int)w; rp.stride = (int)stride; rp.offset = (int)offset;
     rp.above = test_above ? 1 : 0; rp.cap = spread + 1 > 256 ? 256 : (int)(spread + 1);
     rp.nwords = (int)((w + 31) / 32);
+    rp.nstrips = rp.wp / 128;
     const size_t smem = (size_t)kRow8Warps * (rp.nwords + 1) * sizeof(uint32_t);
     const unsigned blocks = (unsigned)((rows + kRow8Warps - 1) / kRow8Warps);
     rowscan8_kernel<<<blocks, kRow8Warps * 32, smem, st>>>(rp);
@@ -228,7 +239,8 @@ int sweep_ctas_per_sm(int nb, int* out) {
     if (it == g_sweep_ctas.end()) {
         int ctas = 0;
         CQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, sweep_kernel<GMODE>, kSweepWarps * 32, smem));
-        if (const char* e = getenv("CHAQSDF_SWEEP_CTAS")) ctas = atoi(e) > 0 ? atoi(e) : ctas;  // tuning override
+        if (const char* e = getenv("CHAQSDF_SWEEP_CTAS"))  // tuning override: fewer resident CTAs (G mode only)
+            if (GMODE && atoi(e) > 0 && atoi(e) < ctas) ctas = atoi(e);
         it = g_sweep_ctas.emplace(key, ctas).first;
     }
     *out = it->second;
@@ -236,7 +248,7 @@ int sweep_ctas_per_sm(int nb, int* out) {
 }
 
 int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
-                 const Tables* tab, uint8_t* d_out, cudaStream_t st) {
+                 const Tables* tab, uint8_t* d_out, void* d_plan, size_t plan_bytes, cudaStream_t st) {
     DevInfo di;
     if (int rc = device_info(&di)) return rc;
     SweepParams p{};
@@ -245,40 +257,64 @@ int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_b
     p.out_begin = (int)out_begin; p.out_end = (int)out_end;
     p.ncg = (int)((w + 31) / 32);
     p.nstrips = (p.ncg + kSweepWarps - 1) / kSweepWarps;
-    p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2; p.nb = sweep_ring_blocks(p.L);
+    p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2;
+    const int nb_s = sweep_ring_blocks(p.L), nb_g = sweep_ring_blocks_g(p.L);
     const long long out_rows = (long long)(out_end - out_begin);
     p.total_rows = (long long)n_img * p.nstrips * out_rows;
     // keep the whole window in shared memory when that still leaves enough warps to hide latency; otherwise
     // stage only the push side and re-read older rows through L1/L2
     int ctas_s = 0, ctas_g = 0;
     bool gmode = false;
-    if (sweep_smem_bytes(p.nb, false) <= (size_t)di.max_smem_optin) {
-        if (int rc = sweep_ctas_per_sm<false>(p.nb, &ctas_s)) return rc;
+    if (sweep_smem_bytes(nb_s, false) <= (size_t)di.max_smem_optin) {
+        if (int rc = sweep_ctas_per_sm<false>(nb_s, &ctas_s)) return rc;
     }
     if (ctas_s * kSweepWarps < 24) {
-        if (int rc = sweep_ctas_per_sm<true>(p.nb, &ctas_g)) return rc;
+        if (int rc = sweep_ctas_per_sm<true>(nb_g, &ctas_g)) return rc;
         gmode = ctas_g > ctas_s;
     }
     if (const char* e = getenv("CHAQSDF_SWEEP_MODE")) {
-        if (e[0] == 'G') { if (int rc = sweep_ctas_per_sm<true>(p.nb, &ctas_g)) return rc; gmode = true; }
+        if (e[0] == 'G') { if (int rc = sweep_ctas_per_sm<true>(nb_g, &ctas_g)) return rc; gmode = true; }
         else if (e[0] == 'S' && ctas_s > 0) gmode = false;
     }
+    p.nb = gmode ? nb_g : nb_s;
     const int ctas = gmode ? ctas_g : ctas_s;
     if (ctas < 1) return fail(CHAQSDF_ERR_CUDA, "banded pass 2 does not fit in shared memory");
-    const long long slots = (long long)di.sms * ctas;
-    int kruns = 1;  // runs per CTA (round-robin); more runs mix cheap and dear areas but re-read more context
-    if (const char* e = getenv("CHAQSDF_SWEEP_RUNS")) kruns = atoi(e) > 0 ? atoi(e) : kruns;
-    long long run = (p.total_rows + slots * kruns - 1) / (slots * kruns);
-    // Fill every resident CTA slot: with all slots busy the time is ~ (run + cost of 2L context rows), which only
-    // falls as runs get shorter; the floor just keeps the per-piece set-up (first block's load latency) amortised.
+    long long slots = (long long)di.sms * ctas;
+    if (slots > kSweepMaxCtas) slots = kSweepMaxCtas;
+    // One run per resident CTA slot. With all slots busy the time is ~ (run + cost of the 2L context rows), which
+    // only falls as runs get shorter; the floor keeps the per-piece set-up (first block's load latency) amortised.
     long long min_run = 64;
     if (min_run > out_rows) min_run = out_rows;
-    if (run < min_run) run = min_run;
-    if (const char* e = getenv("CHAQSDF_BAND_ROWS")) run = atoll(e) > 0 ? atoll(e) : run;
-    p.rows_per_cta = run;
-    const long long nruns = (p.total_rows + run - 1) / run;
-    const unsigned grid = (unsigned)(nruns < slots ? nruns : slots);
-    p.runs_per_cta = (int)((nruns + grid - 1) / grid);
+    long long nruns = (p.total_rows + min_run - 1) / min_run;
+    if (nruns > slots) nruns = slots;
+    const unsigned grid = (unsigned)nruns;
+    p.rows_per_cta = (p.total_rows + nruns - 1) / nruns;
+    p.cuts = nullptr;
+    const char* split = getenv("CHAQSDF_SWEEP_SPLIT");  // "rows": equal rows per CTA (for comparison)
+    if (!(split && split[0] == 'r')) {
+        // equal estimated cost per CTA: cut points from pass 1's busy bytes
+        if (!d_plan || plan_bytes < sweep_plan_bytes(n_img, w, buf_rows)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+        SweepPlanParams q{};
+        q.inter = d_inter; q.rs = p.rs; q.flag_off = p.wp + p.wp / 8;
+        q.buf_rows = (int)buf_rows; q.nstrips = p.nstrips; q.n_img = (int)n_img;
+        q.out_begin = p.out_begin; q.out_end = p.out_end;
+        q.nblk = (int)((buf_rows + 31) / 32);
+        q.b0 = p.out_begin >> 5; q.nbo = ((p.out_end - 1) >> 5) - q.b0 + 1;
+        q.reach = (p.L + 31) / 32;
+        q.pb = (uint8_t*)d_plan;
+        q.cuts = (long long*)((char*)d_plan + align_up(n_img * (size_t)p.nstrips * q.nblk, 256));
+        q.ncta = (int)grid;
+        q.c0 = 1; q.cp = 8; q.ce = 16;
+        if (const char* e = getenv("CHAQSDF_SWEEP_COST")) sscanf(e, "%d,%d,%d", &q.c0, &q.cp, &q.ce);
+        if (q.c0 < 1) q.c0 = 1;
+        const long long nflags = (long long)n_img * q.nblk * q.nstrips;
+        const unsigned gb = (unsigned)((nflags + 255) / 256);
+        sweep_busy_kernel<<<gb, 256, 0, st>>>(q);
+        CQ_LAUNCHED("sweep_busy_kernel", gb, 0);
+        sweep_cuts_kernel<<<1, kPlanThreads, 0, st>>>(q);
+        CQ_LAUNCHED("sweep_cuts_kernel", 1, 0);
+        p.cuts = q.cuts;
+    }
     const size_t smem = sweep_smem_bytes(p.nb, gmode);
     if (gmode) sweep_kernel<true><<<grid, kSweepWarps * 32, smem, st>>>(p);
     else sweep_kernel<false><<<grid, kSweepWarps * 32, smem, st>>>(p);
@@ -309,7 +345,7 @@ size_t chaqsdf_inter_row_bytes(size_t w, size_t spread) {
 
 size_t chaqsdf_batched_workspace_bytes(size_t n, size_t w, size_t h, size_t spread) {
     if (check_dims(w, h, spread) || n == 0) return 0;
-    if (banded(spread)) return align_up(n * h * banded_rs(w), 256);
+    if (banded(spread)) return align_up(n * h * banded_rs(w), 256) + sweep_plan_bytes(n, w, h);
     EnvPlan pl;
     if (plan_envelope(w, h, h, n, cap_for(spread), &pl)) return 0;
     return align_up(n * w * h * sizeof(uint16_t), 256) + pl.ring_bytes;
@@ -319,7 +355,7 @@ size_t chaqsdf_workspace_bytes(size_t w, size_t h, size_t spread) {
 }
 size_t chaqsdf_envelope_workspace_bytes(size_t w, size_t buf_rows, size_t spread) {
     if (check_dims(w, buf_rows, spread)) return 0;
-    if (banded(spread)) return 0;
+    if (banded(spread)) return sweep_plan_bytes(1, w, buf_rows);
     EnvPlan pl;
     if (plan_envelope(w, buf_rows, buf_rows, 1, cap_for(spread), &pl)) return 0;
     return pl.ring_bytes;
@@ -354,7 +390,8 @@ int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size
     if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     if (banded(spread)) {
         if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
-        return launch_sweep((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, (cudaStream_t)stream);
+        return launch_sweep((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
+                            workspace_bytes, (cudaStream_t)stream);
     }
     EnvPlan pl;
     if (int rc = plan_envelope(w, buf_rows, out_end - out_begin, 1, cap_for(spread), &pl)) return rc;
@@ -379,9 +416,11 @@ int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t 
     cudaStream_t st = (cudaStream_t)stream;
     if (banded(spread)) {
         if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
-        if (workspace_bytes < align_up(n * h * banded_rs(w), 256)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+        const size_t inter_bytes = align_up(n * h * banded_rs(w), 256);
+        if (workspace_bytes < inter_bytes + sweep_plan_bytes(n, w, h)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
         if (int rc = launch_rowscan8(d_imgs, w, n * h, stride, offset, test_above, spread, (uint8_t*)d_workspace, st)) return rc;
-        return launch_sweep((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, st);
+        return launch_sweep((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
+                            workspace_bytes - inter_bytes, st);
     }
     const int cap = cap_for(spread);
     EnvPlan pl;

@@ -7,7 +7,8 @@
 //   dist_transform_axis #1   reference openmp/df.c:130 -> df.c:29-97 (for {0,INF} input the lower envelope
 //                            along a row is (x - nearest seed)^2, i.e. a run-length scan)
 // Output record per row (see sweep.cuh): Wp bytes g8 = min(G, C) - 1, then Wp/32 words of class bits
-// (bit = 1: inside, the reference's `true`). G = distance along the row to the nearest pixel of the OTHER
+// (bit = 1: inside, the reference's `true`), then one "busy" byte per 128-column strip (1: some pixel of the
+// strip has an opposite-class pixel within reach along this row) -- a hint for pass 2's work split only. G = distance along the row to the nearest pixel of the OTHER
 // class. The distance is class-agnostic: it is the distance to the nearest class change, so one pair of
 // ramps serves both fields.
 //
@@ -36,6 +37,7 @@ struct RowScan8Params {
     int above;
     int cap;             // C_row = min(spread+1, 256): g8 = min(G, cap) - 1
     int nwords;          // ceil(w/32)
+    int nstrips;         // 128-column strips = wp/128; busy bytes live at record offset wp + wp/8
 };
 
 __global__ void __launch_bounds__(kRow8Warps * 32) rowscan8_kernel(RowScan8Params p) {
@@ -120,6 +122,12 @@ __global__ void __launch_bounds__(kRow8Warps * 32) rowscan8_kernel(RowScan8Param
         const int PR = nr ? sr : look;
         const int tl = __shfl_sync(0xffffffffu, lastL, BL ? 31 - __clz(BL) : 0);
         if (BL) carryL = tl;
+        {   // busy hint: does any of this lane's pixels see a class change within reach? (4 lanes = one strip)
+            const bool busy = nvalid > 0 && ((Lw | R) != 0u || x0 - PL + 1 < cap || PR - (x0 + nvalid - 1) + 1 < cap);
+            const uint32_t B = __ballot_sync(0xffffffffu, busy);
+            const int strip = ch * 8 + lane;
+            if (lane < 8 && strip < p.nstrips) rec[p.wp + (p.wp >> 3) + strip] = ((B >> (4 * lane)) & 0xFu) ? 1 : 0;
+        }
 
         if (nvalid > 0) {
             int dl[32];

@@ -15,9 +15,10 @@
 //
 // Work split: a CTA of kSweepWarps warps owns a strip of 32*kSweepWarps adjacent columns, so its warps read
 // the same 128-byte lines of the record at about the same time. The (image, strip, row) space is linearised
-// and cut into equal runs, one per resident CTA, so a launch is a single wave on 148 SMs whatever the image
-// shape; a run that crosses a strip boundary is finished as two pieces. Each piece re-reads L rows of context
-// above and below itself.
+// and cut into runs of equal estimated cost (sweep_plan.cuh), one per resident CTA, so a launch is a single
+// wave on 148 SMs whatever the image shape; a run that crosses a strip boundary is finished as two pieces.
+// Each piece re-reads L rows of context above and below itself. Blocks of 32 rows in which no column of the
+// warp has anything within reach are skipped (sweep_core.h, note_quiet / emit_quiet_block).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -39,8 +40,8 @@ struct SweepParams {
     int ncg;                 // column groups (32 columns) per image = ceil(w/32)
     int nstrips;             // strips per image = ceil(ncg / kSweepWarps)
     long long total_rows;    // n_img * nstrips * (out_end-out_begin): the linearised work
-    long long rows_per_cta;  // run length
-    int runs_per_cta;        // a CTA takes runs blockIdx.x, blockIdx.x + gridDim.x, ... (mixes cheap and dear areas)
+    long long rows_per_cta;  // run length when there are no cut points
+    const long long* cuts;   // [gridDim.x + 1] cut points of the linearised work (sweep_plan.cuh), or null
     int nb, L, c2;           // ring blocks, lag, clamp
 };
 
@@ -85,6 +86,7 @@ struct SweepCtx {
     uint32_t gring_s;      // shared-space address of the ring (lane 0)
     int nb, lane;
     int gslot;             // GMODE: staging slot of the block being pushed
+    int cur_blk;           // block being pushed
     // current piece
     const uint8_t* rec0;   // record of relative row 0, at this warp's first column (16-byte aligned)
     const uint8_t* cls0;   // class word of relative row 0 for this column group
@@ -136,6 +138,27 @@ struct SweepCtx {
         craw = craw_next;
         craw_next = ldg_cls(blk + 1);
         gpush = gring + slot * 1024;
+        cur_blk = blk;
+    }
+    // the 32x32 bytes of the block being pushed, 8 words per lane (conflict-free), rows past the buffer ignored
+    __device__ __forceinline__ bool block_quiet(int L) const {
+        const uint32_t* wds = reinterpret_cast<const uint32_t*>(gpush - lane);
+        const uint32_t lim = (uint32_t)L * 0x01010101u;
+        const int rows_here = nrows - cur_blk * 32;  // rows of this block that exist (>= 1)
+        uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t v = wds[lane + 32 * i];            // row (lane >> 3) + 4*i, columns 4*(lane & 7)..+3
+            const bool live = (lane >> 3) + 4 * i < rows_here;
+            m = __vminu4(m, live ? v : 0xFFFFFFFFu);
+        }
+        return __all_sync(0xffffffffu, __vcmpgeu4(m, lim) == 0xFFFFFFFFu);
+    }
+    __device__ __forceinline__ bool cls_uniform(uint32_t w, int* bit) const {
+        const bool z = __all_sync(0xffffffffu, w == 0u || !store_ok);
+        const bool o = __all_sync(0xffffffffu, w == 0xFFFFFFFFu || !store_ok);
+        *bit = z ? 0 : 1;
+        return z || o;
     }
     __device__ __forceinline__ uint32_t cls_fetch(int) { return warp_transpose32(craw, lane); }
     __device__ __forceinline__ uint32_t g_push(int j) const { return gpush[j * 32]; }
@@ -173,13 +196,25 @@ struct SweepCtx {
             qhi = qthr[qm + 1];
         }
         if (CQ_UNLIKELY(d2c >= qhi || d2c < qlo || cls != qcls)) requant(cls, d2c);
+        #ifdef CQ_STCS
+        if (store_ok) __stcs(optr, (uint8_t)qbyte);
+#else
         if (store_ok) *optr = (uint8_t)qbyte;
+#endif
         optr += ostride;
+    }
+    __device__ __forceinline__ void out_run(int cls, int d2c, int n) {
+        out(cls, d2c);
+        const uint8_t b = (uint8_t)qbyte;
+        for (int i = 1; i < n; ++i) {
+            if (store_ok) *optr = b;
+            optr += ostride;
+        }
     }
 };
 
 template <bool GMODE>
-__global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 7 : 2) sweep_kernel(SweepParams p) {
+__global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 8 : 2) sweep_kernel(SweepParams p) {
     extern __shared__ __align__(16) uint8_t s_sweep[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int32_t* s_thr = reinterpret_cast<int32_t*>(s_sweep);
@@ -200,9 +235,15 @@ __global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 7 : 2) sweep_kernel(
     c.ostride = p.w;
 
     const int out_rows = p.out_end - p.out_begin;
-    for (int k = 0; k < p.runs_per_cta; ++k) {
-    long long lin = ((long long)k * gridDim.x + blockIdx.x) * p.rows_per_cta;
-    long long lin_end = lin + p.rows_per_cta;
+    {
+    long long lin, lin_end;
+    if (p.cuts) {
+        lin = p.cuts[blockIdx.x];
+        lin_end = p.cuts[blockIdx.x + 1];
+    } else {
+        lin = (long long)blockIdx.x * p.rows_per_cta;
+        lin_end = lin + p.rows_per_cta;
+    }
     if (lin_end > p.total_rows) lin_end = p.total_rows;
     while (lin < lin_end) {
         const long long piece = lin / out_rows;         // (image, strip)

@@ -51,6 +51,11 @@ constexpr int kNoNxtH = 1 << 29;  // height of the absent successor: never bette
 //   uint32_t hull_ld(int slot) / void hull_st(int slot, uint32_t)
 //   uint32_t cls_ld(int slot)  / void cls_st(int slot, uint32_t)
 //   void     out(int cls, int d2c)            next result (rows arrive in order from y0; d2c clamped to C^2)
+//   void     out_run(int cls, int d2c, int n) the next n results are all (cls, d2c)
+//   bool     block_quiet(int L)               no row of the block being pushed holds a g8 < L -- for EVERY column
+//                                             that shares this control flow (the warp on the device), so that
+//                                             skipping the block's pushes is a uniform decision
+//   bool     cls_uniform(uint32_t w, int* b)  the class word w is all-0 or all-1, the same for every such column
 template <class Ctx>
 struct ColumnSweep {
     Ctx& c;
@@ -71,6 +76,9 @@ struct ColumnSweep {
     // eblk < pblk (for eblk == pblk the live register hwp is used).
     int eblk, eslot;
     uint32_t ehw, emask;
+    // quiet tracking: the last qrun pushed blocks (ending with pblk) held no site in any column of the group and
+    // one class (qruncls) throughout
+    int qrun, qruncls, qneed;
 
     CQ_HD ColumnSweep(Ctx& ctx, int nb_, int lag, int c2) : c(ctx), NB(nb_), L(lag), C2(c2) {}
 
@@ -153,6 +161,29 @@ struct ColumnSweep {
         einit = false; ecls = 0; upd = kFarRow; nb = kFarRow;
         cur_p = -1; cur_h = kNoCurH; nxt_p = -1; nxt_h = kNoNxtH;
         eblk = 0; eslot = 0; ehw = 0u; emask = 0xFFFFFFFFu;
+        qrun = 0; qruncls = 0; qneed = (2 * L + 31) / 32 + 1;
+    }
+
+    // after begin_block: is the block free of sites for the whole group, and does it extend a quiet run?
+    CQ_HD bool note_quiet() {
+        const bool pq = c.block_quiet(L);
+        int bit = 0;
+        if (pq && c.cls_uniform(cwp, &bit)) {
+            qrun = (qrun > 0 && bit == qruncls) ? qrun + 1 : 1;
+            qruncls = bit;
+        } else {
+            qrun = 0;
+        }
+        return pq;
+    }
+    // Rows [base-L, base-L+32) when the blocks covering [base-2L, base+31] (or the buffer top) are one quiet run:
+    // no site and no class change within reach of any of them, in any column of the group -> D2 = C^2.
+    CQ_HD bool emit_quiet_ok(int blk) const { return einit && qrun >= cq_min(qneed, blk + 1); }
+    CQ_HD void emit_quiet_block(int e0) {
+        ++upd;
+        if (CQ_UNLIKELY(e0 == nb)) class_flip(e0);  // only possible for L == 0 (row e0-1 is within reach otherwise)
+        upd += 31;
+        c.out_run(ecls, C2, 32);
     }
 
     // a new block of 32 rows starts: retire the previous one to the rings, fetch the class bits of the new one
@@ -313,11 +344,26 @@ struct ColumnSweep {
         const int tend = cq_min(nrows, y1 + L);  // rows [0, tend) are pushed
         const int stop = y1 + L;                 // row er = rr - L is emitted for rr in [y0 + L, stop)
         for (int base = 0; base < stop; base += 32) {
-            if (base < tend) begin_block(base >> 5, base == 0);
+            bool pq = false;  // nothing to push in this block (for the whole group)
+            if (base < tend) {
+                begin_block(base >> 5, base == 0);
+                pq = note_quiet();
+            } else if (qrun > 0) {
+                ++qrun;  // rows past the end of the buffer: no sites, no class change
+            }
             const int jstop = cq_min(32, stop - base);
             const int jpush = cq_max(0, cq_min(jstop, tend - base));
             const int jemit = cq_max(0, cq_min(jstop, y0 + L - base));
+            if (jemit == 0 && jstop == 32 && (jpush == 32 || jpush == 0) && emit_quiet_ok(base >> 5)) {
+                emit_quiet_block(base - L);
+                continue;
+            }
             const int lo = cq_min(jpush, jemit), hi = cq_max(jpush, jemit);
+            if (pq) {  // same as pushing 32 rows that hold no site
+                if (!einit && jemit < jstop) init_emit(y0);
+                rows<false, true>(base, jemit, jstop);
+                continue;
+            }
             rows<true, false>(base, 0, lo);
             if (!einit && jemit < jstop) init_emit(y0);
             if (jemit < jpush) rows<true, true>(base, lo, hi);
@@ -328,5 +374,8 @@ struct ColumnSweep {
 
 // ring blocks needed: rows [t-2L-31, t] stay addressable while the next block (32 rows) is being prefetched
 CQ_HD int sweep_ring_blocks(int L) { return (2 * L + 64 + 31) / 32; }
+// when g8 is not kept in the ring (re-read from global memory), the hull/class rings only span the blocks
+// that can still hold a site, floor((32*pblk - 2L)/32) .. pblk
+CQ_HD int sweep_ring_blocks_g(int L) { return (2 * L + 31) / 32 + 1; }
 
 }  // namespace chaq

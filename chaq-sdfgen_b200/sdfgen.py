@@ -7,7 +7,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libchaqsdf_b200.so")
+LIB_PATH = os.environ.get("CHAQSDF_LIB") or os.path.join(HERE, "libchaqsdf_b200.so")  # override: A/B builds only
 _lib = None
 
 

@@ -36,7 +36,9 @@ struct Ctx2 {
     int* d2; uint8_t* ocls; int y0;
     long oob = 0;
     int cur_slot = 0, nout = 0;
+    int Lg = 0;
     void block_begin(int blk, int slot) {
+        cur_blk = blk;
         cur_slot = slot;
         slot_blk[slot] = blk;
         slot_blk[(slot + 1) % NB] = blk + 1;  // the prefetch of the next block lands there now
@@ -50,8 +52,15 @@ struct Ctx2 {
         }
         return wd;
     }
-    uint32_t g_push(int j) { return g_at(slot_blk[cur_slot], cur_slot, j); }
+    bool gmode = false;  // g8 re-read from "global memory" by block number; only hull/class live in rings
+    int cur_blk = 0;
+    uint32_t g_push(int j) { return g_at(gmode ? cur_blk : slot_blk[cur_slot], cur_slot, j); }
     uint32_t g_at(int blk, int slot, int j) {
+        if (gmode) {
+            const int r = blk * 32 + j;
+            if (r < 0 || r >= nrows || blk > cur_blk || blk * 32 + 31 < cur_blk * 32 - 2 * Lg) { ++oob; return 0; }
+            return gcol[(size_t)r * stride];
+        }
         if (slot < 0 || slot >= NB) { ++oob; return 0; }
         if (slot_blk[slot] != blk) ++oob;  // the ring no longer holds that block
         int r = slot_blk[slot] * 32 + j;
@@ -63,13 +72,24 @@ struct Ctx2 {
     uint32_t cls_ld(int s) { if (s < 0 || s >= NB) { ++oob; return 0; } return cls[s]; }
     void cls_st(int s, uint32_t v) { if (s < 0 || s >= NB) { ++oob; return; } cls[s] = v; }
     void out(int c, int v) { d2[nout] = v; ocls[nout] = (uint8_t)c; ++nout; }
+    void out_run(int c, int v, int n) { for (int i = 0; i < n; ++i) out(c, v); }
+    // the group that shares control flow is this one column
+    bool block_quiet(int L) {
+        const int blk = cur_blk;
+        for (int j = 0; j < 32; ++j) {
+            const int r = blk * 32 + j;
+            if (r < nrows && gcol[(size_t)r * stride] < L) return false;
+        }
+        return true;
+    }
+    bool cls_uniform(uint32_t w, int* bit) { *bit = w ? 1 : 0; return w == 0u || w == 0xFFFFFFFFu; }
 };
 
 // mask: h*w bytes of 0/1. band_rows: split each column into bands finished independently (0 = one band).
 // Outputs: the byte image; optionally the clamped squared distances and classes. Returns 0, or 1000+n on
 // out-of-range ring/row accesses.
 extern "C" int emul2_sdf(const uint8_t* mask, int w, int h, size_t spread, int asym, int band_rows, uint8_t* out,
-                         int32_t* d2_out, int* cap_eff) {
+                         int32_t* d2_out, int* cap_eff, int gmode) {
     QuantTable q; build_quant_table(spread, asym, &q);
     LevelTable lt; build_level_table(q, &lt);
     const int C = lt.cap_eff, L = C - 1;
@@ -78,7 +98,7 @@ extern "C" int emul2_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
     std::vector<uint8_t> g8;
     rowscan_naive(mask, w, h, C, g8);
     if (band_rows <= 0) band_rows = h;
-    const int NB = sweep_ring_blocks(L);
+    const int NB = gmode ? sweep_ring_blocks_g(L) : sweep_ring_blocks(L);
     std::vector<int> cd2(h); std::vector<uint8_t> ccls(h);
     for (int x = 0; x < w; ++x) {
         for (int y0 = 0; y0 < h; y0 += band_rows) {
@@ -86,7 +106,7 @@ extern "C" int emul2_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
             const int row0 = (y0 - L > 0 ? y0 - L : 0) & ~31;
             Ctx2 c;
             c.gcol = g8.data() + (size_t)row0 * w + x; c.mcol = mask + (size_t)row0 * w + x; c.stride = (size_t)w;
-            c.nrows = h - row0; c.NB = NB;
+            c.nrows = h - row0; c.NB = NB; c.gmode = gmode != 0; c.Lg = L;
             c.slot_blk.assign(NB, -1000000);
             c.hull.assign(NB, 0xdeadbeefu); c.cls.assign(NB, 0xdeadbeefu);
             c.d2 = cd2.data() + y0; c.ocls = ccls.data() + y0; c.y0 = y0 - row0;

@@ -207,15 +207,22 @@ def emul2(tmp_path_factory):
                     os.path.join(ROOT, "tests", "emul", "emul2.cpp")], check=True)
     L = C.CDLL(so)
     u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
-    L.emul2_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, u8p, C.c_void_p, C.POINTER(C.c_int)]
+    L.emul2_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, u8p, C.c_void_p, C.POINTER(C.c_int), C.c_int]
     return L
 
 
-def _emul2_u8(L, mask, spread, asym, band):
+def _emul2_u8(L, mask, spread, asym, band, gmode=None):
+    """gmode None: run both ring modes (S: g8 in the ring, G: g8 re-read, shorter hull/class rings) and require
+    identical results."""
+    if gmode is None:
+        a, ce = _emul2_u8(L, mask, spread, asym, band, 0)
+        b, _ = _emul2_u8(L, mask, spread, asym, band, 1)
+        assert np.array_equal(a, b), "ring modes S and G disagree"
+        return a, ce
     h, w = mask.shape
     out = np.empty((h, w), np.uint8)
     ce = C.c_int()
-    rc = L.emul2_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), band, out, None, C.byref(ce))
+    rc = L.emul2_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), band, out, None, C.byref(ce), gmode)
     assert rc == 0, f"emulated banded pass failed (rc={rc}: 1 = cap_eff > 256, 2 = row count, >=1000 = stale ring access)"
     return out, ce.value
 
