@@ -214,7 +214,7 @@ struct SweepCtx {
 };
 
 template <bool GMODE>
-__global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 8 : 2) sweep_kernel(SweepParams p) {
+__global__ void __launch_bounds__(kSweepWarps * 32, GMODE ? 7 : 2) sweep_kernel(SweepParams p) {
     extern __shared__ __align__(16) uint8_t s_sweep[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int32_t* s_thr = reinterpret_cast<int32_t*>(s_sweep);
