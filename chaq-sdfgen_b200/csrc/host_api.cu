@@ -5,9 +5,11 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/chaqsdf.h"
 
@@ -25,6 +27,8 @@ struct Pool {
     void* buf[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t cap[4] = {0, 0, 0, 0};
     cudaStream_t stream = nullptr;
+    cudaStream_t s_in = nullptr, s_out = nullptr;  // copy streams of the banded pipeline
+    std::vector<cudaEvent_t> ev;                   // grow-only event cache
     int* flag = nullptr;
 };
 Pool g_pool;
@@ -36,6 +40,7 @@ cudaError_t pool_get(int slot, size_t bytes, void** out) {
     if (g_pool.dev != dev) {  // device changed: drop everything (buffers belong to the old device)
         for (int i = 0; i < 4; ++i) { g_pool.buf[i] = nullptr; g_pool.cap[i] = 0; }
         g_pool.stream = nullptr; g_pool.flag = nullptr;
+        g_pool.s_in = g_pool.s_out = nullptr; g_pool.ev.clear();
         g_pool.dev = dev;
     }
     if (!g_pool.stream) {
@@ -53,6 +58,92 @@ cudaError_t pool_get(int slot, size_t bytes, void** out) {
     }
     *out = g_pool.buf[slot];
     return cudaSuccess;
+}
+
+cudaError_t pool_events(size_t n) {
+    while (g_pool.ev.size() < n) {
+        cudaEvent_t e;
+        cudaError_t r = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        if (r != cudaSuccess) return r;
+        g_pool.ev.push_back(e);
+    }
+    return cudaSuccess;
+}
+
+// Host buffers, banded path: the image goes through in row bands so that the upload of band k+1, the kernels of
+// band k and the download of band k-1 overlap (three streams). Pass 1 is per row; pass 2 of output rows
+// [done, b - spread) only needs pass 1 up to row b, and a sub-buffer starting >= spread rows above `done` (both
+// are the exact-context rule of chaqsdf_envelope_device). Results are identical to the one-shot path.
+// Band heights: short bands first (the download can start early) and last (little is left to do once the upload
+// ends), `cap` rows in between (large launches of pass 2 waste less on the context rows of each piece).
+std::vector<size_t> pipeline_bands(size_t h, size_t cap, size_t first) {
+    std::vector<size_t> up, down, v;
+    size_t rem = h;
+    for (size_t s = first; s < cap && rem > 4 * s; s *= 2) { up.push_back(s); rem -= s; }
+    size_t dsum = 0;
+    for (size_t t = first; t < cap && dsum + t < rem / 2; t *= 2) { down.push_back(t); dsum += t; }
+    const size_t mid = rem - dsum;
+    const size_t nmid = (mid + cap - 1) / cap;
+    v = up;
+    size_t left = mid;
+    for (size_t i = 0; i < nmid; ++i) {
+        size_t b = ((mid / nmid) + 31) & ~(size_t)31;
+        if (i + 1 == nmid || b > left) b = left;
+        if (b) v.push_back(b);
+        left -= b;
+    }
+    for (size_t i = down.size(); i-- > 0;) v.push_back(down[i]);
+    return v;
+}
+
+int u8_pipelined(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above, size_t spread,
+                 int asymmetric, uint8_t* out, size_t band_rows, size_t first_rows) {
+    const size_t rs = chaqsdf_inter_row_bytes(w, spread);
+    const size_t plan_bytes = chaqsdf_envelope_workspace_bytes(w, h, spread);
+    void *d_img, *d_out, *d_inter, *d_plan;
+    if (pool_get(0, w * h * stride, &d_img) != cudaSuccess || pool_get(1, w * h, &d_out) != cudaSuccess ||
+        pool_get(2, rs * h, &d_inter) != cudaSuccess || pool_get(3, plan_bytes ? plan_bytes : 256, &d_plan) != cudaSuccess)
+        return set_error(CHAQSDF_ERR_CUDA, "device allocation failed");
+    if (!g_pool.s_in) {
+        if (cudaStreamCreateWithFlags(&g_pool.s_in, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&g_pool.s_out, cudaStreamNonBlocking) != cudaSuccess)
+            return set_error(CHAQSDF_ERR_CUDA, "stream creation failed");
+    }
+    const std::vector<size_t> bands = pipeline_bands(h, band_rows, first_rows);
+    const size_t nbands = bands.size();
+    if (pool_events(2 * nbands) != cudaSuccess) return set_error(CHAQSDF_ERR_CUDA, "event creation failed");
+    cudaStream_t s_in = g_pool.s_in, s_cmp = g_pool.stream, s_out = g_pool.s_out;
+    const uint8_t* dimg = (const uint8_t*)d_img;
+    uint8_t* dinter = (uint8_t*)d_inter;
+    uint8_t* dout = (uint8_t*)d_out;
+    size_t done = 0;  // output rows [0, done) are computed
+    size_t a = 0, b = 0;
+    for (size_t k = 0; k < nbands; ++k) {
+        a = b; b = a + bands[k];
+        cudaEvent_t ev_in = g_pool.ev[2 * k], ev_cmp = g_pool.ev[2 * k + 1];
+        const size_t row_bytes = w * stride;
+        if (cudaMemcpyAsync((void*)(dimg + a * row_bytes), img + a * row_bytes, (b - a) * row_bytes, cudaMemcpyHostToDevice,
+                            s_in) != cudaSuccess || cudaEventRecord(ev_in, s_in) != cudaSuccess ||
+            cudaStreamWaitEvent(s_cmp, ev_in, 0) != cudaSuccess)
+            return set_error(CHAQSDF_ERR_CUDA, "upload failed");
+        int rc = chaqsdf_rowscan_device(dimg + a * row_bytes, w, b - a, stride, offset, test_above, spread, dinter + a * rs, s_cmp);
+        if (rc) return rc;
+        const size_t upto = b == h ? h : (b > spread ? b - spread : 0);
+        if (upto > done) {
+            size_t top = done > spread ? done - spread : 0;
+            top &= ~(size_t)31;
+            rc = chaqsdf_envelope_device(dinter + top * rs, w, b - top, done - top, upto - top, spread, asymmetric,
+                                         dout + done * w, d_plan, plan_bytes, s_cmp);
+            if (rc) return rc;
+            if (cudaEventRecord(ev_cmp, s_cmp) != cudaSuccess || cudaStreamWaitEvent(s_out, ev_cmp, 0) != cudaSuccess ||
+                cudaMemcpyAsync(out + done * w, dout + done * w, (upto - done) * w, cudaMemcpyDeviceToHost, s_out) != cudaSuccess)
+                return set_error(CHAQSDF_ERR_CUDA, "download failed");
+            done = upto;
+        }
+    }
+    if (cudaStreamSynchronize(s_out) != cudaSuccess || cudaStreamSynchronize(s_cmp) != cudaSuccess)
+        return set_error(CHAQSDF_ERR_CUDA, "pipeline failed");
+    return CHAQSDF_OK;
 }
 
 // {0,+INF} float heights -> 255/0 mask bytes; anything else raises the flag (general heights: not this path)
@@ -84,6 +175,21 @@ int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t off
     const size_t ws_bytes = chaqsdf_workspace_bytes(w, h, spread);
     if (ws_bytes == 0) return CHAQSDF_ERR_CUDA;  // error string already set by the planner
     std::lock_guard<std::mutex> lk(g_pool.mu);
+    // large images on the banded path: overlap upload, kernels and download band by band
+    if (spread <= 256 && w * h >= ((size_t)1 << 22)) {
+        size_t band = ((size_t)64 << 20) / (w * stride);  // ~64 MB of input per band
+        if (const char* e = getenv("CHAQSDF_PIPE_ROWS")) band = (size_t)atoll(e);
+        band = (band + 31) & ~(size_t)31;
+        if (band < 2 * spread + 64) band = (2 * spread + 64 + 31) & ~(size_t)31;
+        size_t first = ((size_t)16 << 20) / (w * stride);  // ~16 MB first/last band
+        if (const char* e = getenv("CHAQSDF_PIPE_FIRST")) first = (size_t)atoll(e);
+        first = (first + 31) & ~(size_t)31;
+        if (first < spread + 32) first = (spread + 32 + 31) & ~(size_t)31;
+        if (first > band) first = band;
+        if (band > 0 && band * 2 <= h) {
+            return u8_pipelined(img, w, h, stride, offset, test_above, spread, asymmetric, out, band, first);
+        }
+    }
     void *d_img, *d_out, *d_ws;
     const size_t in_bytes = w * h * stride, out_bytes = w * h;
     if (pool_get(0, in_bytes, &d_img) != cudaSuccess || pool_get(1, out_bytes, &d_out) != cudaSuccess ||

@@ -220,6 +220,25 @@ def test_config4_full_size(pkg, oracle):
     assert np.array_equal(gt, want.T)
 
 
+def test_host_api_pipelined_bands(pkg, oracle, monkeypatch):
+    """chaqsdf_u8 on a large image goes through in row bands (upload / kernels / download overlapped); the result
+    must not depend on the band height, including bands barely taller than the context they need."""
+    n, spread = 2048, 40
+    img = oracle.syn_discs(n)
+    want = oracle.sdf(img, n, n, spread=spread)
+    for rows in ("160", "352", "1000"):
+        monkeypatch.setenv("CHAQSDF_PIPE_ROWS", rows)
+        assert np.array_equal(pkg.sdf_u8(img, n, n, spread=spread), want), rows
+    # interleaved (Y,A) input, asymmetric, pinned buffers
+    ya = np.ascontiguousarray(np.stack([255 - img, img], axis=-1))
+    monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "224")
+    hin, hout = torch.from_numpy(ya).pin_memory(), torch.empty((n, n), dtype=torch.uint8).pin_memory()
+    pkg.sdf_u8(hin, n, n, stride=2, offset=1, spread=spread, asymmetric=True, out=hout)
+    assert np.array_equal(hout.numpy(), oracle.sdf(img, n, n, spread=spread, asymmetric=True))
+    monkeypatch.delenv("CHAQSDF_PIPE_ROWS")
+    assert np.array_equal(pkg.sdf_u8(img, n, n, spread=spread), want)
+
+
 def test_error_paths(pkg):
     d = torch.zeros((8, 8), dtype=torch.uint8, device="cuda")
     with pytest.raises(pkg.ChaqSdfError):
