@@ -194,7 +194,7 @@ def run_ours(args, rank, world, local_rank):
             return out
     else:
         def step(ev=None):
-            return pkg.sdf_u8_sharded(d_band, w, h, SPREAD, False, rank, world, None, state)
+            return pkg.sdf_u8_sharded(d_band, w, h, SPREAD, False, rank, world, None, state, events=ev)
 
     for _ in range(W):
         step()
@@ -202,22 +202,26 @@ def run_ours(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3 if world == 1 else 4)] for _ in range(K)]
     l0 = pkg.launch_count()
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t_start.record()
     for k in range(K):
-        res = step(evs[k] if world == 1 else None)
+        res = step(evs[k])
     t_end.record()
     barrier()
     launches = pkg.launch_count() - l0
     clocks = sampler.stop() if rank == 0 else None
     ms_total = t_start.elapsed_time(t_end)
+    phases = None
     if dist is not None:
-        t = torch.tensor([ms_total], device=dev)
+        ph = [float(np.mean([e[i].elapsed_time(e[i + 1]) for e in evs])) for i in range(3)]
+        t = torch.tensor([ms_total] + ph, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
+        ms_total = float(t[0].item())
+        phases = {"rowscan_ms": float(t[1]), "halo_exchange_ms": float(t[2]), "envelope_ms": float(t[3]),
+                  "note": "per-phase CUDA-event means, max over ranks"}
     ms_step = ms_total / K
     value = h * w / (ms_step * 1e-3) / 1e6
 
@@ -290,7 +294,7 @@ def run_ours(args, rank, world, local_rank):
                        "1.125 B/px intermediate (NCCL p2p)" if world > 1 else ""),
                        "l2": "inputs larger than L2 (268 MB mask + 302 MB intermediate + 268 MB bitmap per step vs "
                              "126 MB L2)"},
-            "roofline": roofline, "passes": passes, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "passes": passes, "phases": phases, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks}
     print(json.dumps(line), flush=True)
     if dist is not None:

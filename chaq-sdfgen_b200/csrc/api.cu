@@ -18,6 +18,7 @@
 #include "rowscan8.cuh"
 #include "sweep.cuh"
 #include "sweep_plan.cuh"
+#include "hull.cuh"
 
 using namespace chaq;
 
@@ -120,10 +121,17 @@ size_t banded_rs(size_t w) {
     const size_t wp = (size_t)banded_wp(w);
     return wp + wp / 8 + align_up(wp / 128, 16);
 }
-// scratch of the banded pass 2's work split (sweep_plan.cuh): block-busy bytes + cut points
+// scratch of the banded pass 2: the hull bitmask + block flags of build/merge/emit (hull.cuh), or the work split
+// of the single-sweep variant (sweep_plan.cuh: block-busy bytes + cut points); sized for either
+size_t hull_words_bytes(size_t n_img, size_t w, size_t buf_rows) {
+    const size_t ncg = (w + 31) / 32, nblk = (buf_rows + 31) / 32;
+    return align_up(n_img * nblk * ncg * 32 * sizeof(uint32_t), 256);
+}
 size_t sweep_plan_bytes(size_t n_img, size_t w, size_t buf_rows) {
-    const size_t nstrips = (size_t)banded_wp(w) / 128, nblk = (buf_rows + 31) / 32;
-    return align_up(n_img * nstrips * nblk, 256) + align_up((size_t)(kSweepMaxCtas + 1) * sizeof(long long), 256);
+    const size_t nstrips = (size_t)banded_wp(w) / 128, nblk = (buf_rows + 31) / 32, ncg = (w + 31) / 32;
+    const size_t plan = align_up(n_img * nstrips * nblk, 256) + align_up((size_t)(kSweepMaxCtas + 1) * sizeof(long long), 256);
+    const size_t hull = hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256);
+    return plan > hull ? plan : hull;
 }
 size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w) : w * sizeof(uint16_t); }
 
@@ -322,6 +330,78 @@ int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_b
     return CHAQSDF_OK;
 }
 
+// banded pass 2 as build / merge / emit (hull.cuh)
+int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
+                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st) {
+    DevInfo di;
+    if (int rc = device_info(&di)) return rc;
+    if (!d_ws || ws_bytes < sweep_plan_bytes(n_img, w, buf_rows)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+    HullParams p{};
+    p.inter = d_inter; p.out = d_out; p.table = tab->dl;
+    p.hull = (uint32_t*)d_ws;
+    p.flags = (uint8_t*)d_ws + hull_words_bytes(n_img, w, buf_rows);
+    p.rs = (long long)banded_rs(w); p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
+    p.nblk = (int)((buf_rows + 31) / 32);
+    p.ncg = (int)((w + 31) / 32); p.wc = p.ncg * 32;
+    p.nstrips = (p.ncg + kHullWarps - 1) / kHullWarps; p.n_img = (int)n_img;
+    p.out_begin = (int)out_begin; p.out_end = (int)out_end;
+    p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2;
+    // run lengths: enough CTAs to fill the machine a few times over, runs no longer than 512 rows (build) / 1024 (emit)
+    const long long target = (long long)di.sms * 24;
+    const long long strips = (long long)n_img * p.nstrips;
+    long long pb = (strips * p.nblk + target - 1) / target;
+    pb = pb < 2 ? 2 : (pb > 16 ? 16 : pb);
+    // runs of >= 2L rows need only two rounds of junction repair; shorter runs cost more in rounds than they gain
+    const long long pb_par = (2 * p.L + 31) / 32;
+    if (pb < pb_par) pb = pb_par;
+    if (const char* e = getenv("CHAQSDF_HULL_PB")) pb = atoll(e);
+    if (pb < 1) pb = 1;
+    if (pb > kHullMaxPieceBlocks) pb = kHullMaxPieceBlocks;
+    if (pb > p.nblk) pb = p.nblk;
+    p.pb = (int)pb; p.nruns_b = (p.nblk + p.pb - 1) / p.pb;
+    const int bfirst = p.out_begin >> 5, nbo = ((p.out_end - 1) >> 5) - bfirst + 1;
+    long long eb = (strips * nbo + target - 1) / target;
+    eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
+    if (const char* e = getenv("CHAQSDF_HULL_EB")) eb = atoll(e);
+    if (eb < 1) eb = 1;
+    if (eb > nbo) eb = nbo;
+    p.eb = (int)eb; p.nruns_e = (nbo + p.eb - 1) / p.eb;
+    const long long gb = strips * p.nruns_b, ge = strips * p.nruns_e;
+    if (gb > 0x7fffffffLL || ge > 0x7fffffffLL) return fail(CHAQSDF_ERR_ARG, "too many runs for one grid");
+    const size_t smem_b = hull_build_smem(p.pb), smem_e = hull_emit_smem();
+    hull_build_kernel<<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
+    CQ_LAUNCHED("hull_build_kernel", gb, smem_b);
+    if (p.nruns_b > 1 && !getenv("CHAQSDF_HULL_SEQ")) {
+        const int njun = p.nruns_b - 1;
+        int nphase = (4 * p.L + p.pb * 32 - 1) / (p.pb * 32);  // same-launch junctions are >= 4L rows apart
+        nphase = nphase < 1 ? 1 : (nphase > njun ? njun : nphase);
+        p.merge_nphase = nphase;
+        for (int phase = 0; phase < nphase; ++phase) {
+            const int nmine = (njun - phase + nphase - 1) / nphase;
+            if (nmine <= 0) continue;
+            p.merge_phase = phase;
+            const long long thr = (long long)n_img * nmine * p.w;
+            const unsigned gm = (unsigned)((thr + 255) / 256);
+            hull_merge_par_kernel<<<gm, 256, 0, st>>>(p);
+            CQ_LAUNCHED("hull_merge_par_kernel", gm, 0);
+        }
+    } else if (p.nruns_b > 1) {
+        const long long cols = (long long)n_img * p.w;
+        const unsigned gm = (unsigned)((cols + 255) / 256);
+        hull_merge_kernel<<<gm, 256, 0, st>>>(p);
+        CQ_LAUNCHED("hull_merge_kernel", gm, 0);
+    }
+    hull_emit_kernel<<<(unsigned)ge, kHullWarps * 32, smem_e, st>>>(p);
+    CQ_LAUNCHED("hull_emit_kernel", ge, smem_e);
+    return CHAQSDF_OK;
+}
+
+// which organisation of the banded pass 2 runs: build/merge/emit (default) or the single sweep
+bool use_hull() {
+    const char* e = getenv("CHAQSDF_PASS2");
+    return !(e && e[0] == 's');
+}
+
 }  // namespace
 
 namespace chaq {
@@ -390,6 +470,9 @@ int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size
     if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     if (banded(spread)) {
         if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
+        if (use_hull())
+            return launch_hull((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
+                               workspace_bytes, (cudaStream_t)stream);
         return launch_sweep((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
                             workspace_bytes, (cudaStream_t)stream);
     }
@@ -419,6 +502,9 @@ int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t 
         const size_t inter_bytes = align_up(n * h * banded_rs(w), 256);
         if (workspace_bytes < inter_bytes + sweep_plan_bytes(n, w, h)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
         if (int rc = launch_rowscan8(d_imgs, w, n * h, stride, offset, test_above, spread, (uint8_t*)d_workspace, st)) return rc;
+        if (use_hull())
+            return launch_hull((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
+                               workspace_bytes - inter_bytes, st);
         return launch_sweep((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
                             workspace_bytes - inter_bytes, st);
     }

@@ -1,0 +1,286 @@
+// hull.cuh -- pass 2, banded fast path (spread <= 256), organised as build / merge / emit over a hull bitmask in
+// global memory (hull_core.h). Replaces dist_transform_axis #2 (reference openmp/df.c:133 -> df.c:29-97, incl.
+// the sqrtf at df.c:95) for the inside and the outside field of openmp/sdfgen.c:277-289, and fuses
+// transform_float_sub (sdfgen.c:98-106) and transform_float_to_byte (sdfgen.c:75-96) as an exact integer
+// threshold look-up (tables.h).
+//
+//   hull_build_kernel  CTA = 4 warps = one 128-column strip x one run of <= 512 rows; lane = column. g8 rows
+//                      arrive by cp.async (16-byte copies, one 32-row block per group, one block ahead); the
+//                      run's hull words live in shared memory until the run is done, then go out as 128-byte
+//                      lines. No context rows: a run only pushes its own rows. Also leaves one flag per
+//                      (block, 32-column group): 0/1 = no site and all class 0/1, 2 = anything else.
+//   hull_merge_kernel  thread = column; repairs the junctions between runs top to bottom.
+//   hull_emit_kernel   CTA = 4 warps = one strip x one run of output rows; walks the finished hull with a
+//                      cursor (hull words and g8 through L1/L2), tracks the in-column class run, quantises,
+//                      and writes whole blocks at once where the flags say nothing is within reach.
+// Grids are one CTA per run (thousands), so the hardware scheduler balances dense and empty areas.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "hull_core.h"
+#include "sweep.cuh"  // cp_async16, cp_async_commit, cp_async_wait1, warp_transpose32, smem_u32, kSweepTableBytes
+#include "tables.h"
+
+namespace chaq {
+
+constexpr int kHullWarps = 4;
+
+struct HullParams {
+    const uint8_t* inter;    // banded intermediate, [n_img][buf_rows] records
+    uint8_t* out;            // [n_img][out_end-out_begin][w]
+    const LevelTable* table;
+    uint32_t* hull;          // [n_img][nblk][wc] hull words
+    uint8_t* flags;          // [n_img][nblk][ncg] block flags
+    long long rs;            // record stride
+    int wp, w, buf_rows, nblk;
+    int wc;                  // ncg * 32
+    int ncg, nstrips, n_img;
+    int out_begin, out_end;
+    int pb;                  // blocks per build run
+    int nruns_b;             // build runs per strip
+    int eb;                  // blocks per emit run
+    int nruns_e;             // emit runs per strip
+    int L, c2;
+    int merge_phase, merge_nphase;  // parallel merge: this launch repairs junctions k = 1 + phase + i*nphase
+};
+
+__host__ __device__ inline size_t hull_build_smem(int pb) { return (size_t)kHullWarps * (2 * 1024 + (size_t)pb * 128); }
+__host__ __device__ inline size_t hull_emit_smem() { return kSweepTableBytes + (size_t)kHullWarps * kClsRing * 128; }
+
+struct HullBuildCtx {
+    const uint8_t* gst;      // staging (2 blocks of 32 rows x 32 bytes), generic pointer at lane 0
+    uint32_t gst_s;          // the same, shared-space address
+    uint32_t* bits;          // run's hull words, already offset by lane
+    const uint8_t* rec0;     // record of buffer row 0 at this warp's first column
+    const uint8_t* rec_lane; // rec0 + lane
+    const uint8_t* cls0;     // class word of buffer row 0 for this column group
+    uint8_t* flag0;          // flags of block 0 for this column group (stride ncg per block)
+    long long rs;
+    unsigned rs32;
+    uint32_t vm;             // columns of the group that exist
+    int nrows, lane, cur_blk, slot, blk_end, blk_first, ncg;
+    uint32_t craw;           // class word of row cur_blk*32 + lane
+
+    __device__ __forceinline__ void issue(int blk, int s) {
+        if (blk < blk_end) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int q = lane + 32 * i, row = q >> 1, half = q & 1;
+                const int r = blk * 32 + row;
+                if (r < nrows) cp_async16(gst_s + s * 1024 + row * 32 + half * 16, rec0 + (long long)r * rs + half * 16);
+            }
+        }
+        cp_async_commit();
+    }
+    __device__ __forceinline__ void block_begin(int blk) {
+        __syncwarp();
+        if (blk == blk_first) { slot = 0; issue(blk, 0); } else slot ^= 1;
+        issue(blk + 1, slot ^ 1);
+        int r = blk * 32 + lane;
+        r = r < nrows ? r : nrows - 1;
+        craw = __ldg(reinterpret_cast<const uint32_t*>(cls0 + (long long)r * rs));
+        cp_async_wait1();
+        __syncwarp();
+        cur_blk = blk;
+    }
+    __device__ __forceinline__ bool block_quiet(int L) const {
+        const uint32_t* wds = reinterpret_cast<const uint32_t*>(gst + slot * 1024);
+        const uint32_t lim = (uint32_t)L * 0x01010101u;
+        const int rows_here = nrows - cur_blk * 32;
+        uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t v = wds[lane + 32 * i];
+            const bool live = (lane >> 3) + 4 * i < rows_here;
+            m = __vminu4(m, live ? v : 0xFFFFFFFFu);
+        }
+        return __all_sync(0xffffffffu, __vcmpgeu4(m, lim) == 0xFFFFFFFFu);
+    }
+    __device__ __forceinline__ uint32_t g_push(int j) const { return gst[slot * 1024 + j * 32 + lane]; }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_lane + (unsigned)r * rs32); }
+    __device__ __forceinline__ uint32_t bits_ld(int i) const { return bits[i * 32]; }
+    __device__ __forceinline__ void bits_st(int i, uint32_t v) { bits[i * 32] = v; }
+    __device__ __forceinline__ void block_end(int blk, uint32_t word) {
+        const bool any = __any_sync(0xffffffffu, word != 0u);
+        const bool all0 = __all_sync(0xffffffffu, (craw & vm) == 0u);
+        const bool all1 = __all_sync(0xffffffffu, (craw & vm) == vm);
+        if (lane == 0) flag0[(long long)blk * ncg] = any ? 2 : (all0 ? 0 : (all1 ? 1 : 2));
+    }
+};
+
+__global__ void __launch_bounds__(kHullWarps * 32) hull_build_kernel(HullParams p) {
+    extern __shared__ __align__(16) uint8_t s_hull[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    long long id = blockIdx.x;
+    const int run = (int)(id % p.nruns_b); id /= p.nruns_b;
+    const int strip = (int)(id % p.nstrips);
+    const int img = (int)(id / p.nstrips);
+    const int cg = strip * kHullWarps + warp;
+    if (cg >= p.ncg) return;  // whole warp; no block-level barrier below
+    uint8_t* base = s_hull + (size_t)warp * (2 * 1024 + (size_t)p.pb * 128);
+    HullBuildCtx c;
+    c.gst = base; c.gst_s = smem_u32(base);
+    c.bits = reinterpret_cast<uint32_t*>(base + 2048) + lane;
+    const uint8_t* recbase = p.inter + (long long)img * p.buf_rows * p.rs;
+    c.rec0 = recbase + cg * 32; c.rec_lane = c.rec0 + lane; c.cls0 = recbase + p.wp + cg * 4;
+    c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
+    c.rs = p.rs; c.rs32 = (unsigned)p.rs;
+    const int ncol = p.w - cg * 32;
+    c.vm = ncol >= 32 ? 0xFFFFFFFFu : ((1u << ncol) - 1u);
+    c.nrows = p.buf_rows; c.lane = lane; c.ncg = p.ncg; c.cur_blk = 0; c.slot = 0;
+    const int b0 = run * p.pb, b1 = b0 + p.pb < p.nblk ? b0 + p.pb : p.nblk;
+    c.blk_first = b0; c.blk_end = b1;
+    int lag = p.L;
+    asm volatile("" : "+r"(lag));
+    HullBuild<HullBuildCtx> hb(c, lag);
+    hb.run(b0, b1, p.buf_rows);
+    uint32_t* hw = p.hull + ((long long)img * p.nblk + b0) * p.wc + cg * 32 + lane;
+    for (int i = 0; i < b1 - b0; ++i) hw[(long long)i * p.wc] = c.bits[i * 32];
+}
+
+struct HullMergeCtx {
+    uint32_t* hcol;          // hull word of block 0 of this column (stride wc per block)
+    const uint8_t* rec_x;    // g8 of buffer row 0 of this column
+    unsigned rs32;
+    int wc;
+    __device__ __forceinline__ uint32_t h_ld(int b) const { return hcol[(long long)b * wc]; }
+    __device__ __forceinline__ void h_st(int b, uint32_t v) { hcol[(long long)b * wc] = v; }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_x + (unsigned)r * rs32); }
+};
+
+__global__ void __launch_bounds__(256) hull_merge_kernel(HullParams p) {
+    const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (t >= (long long)p.n_img * p.w) return;
+    const int img = (int)(t / p.w), x = (int)(t - (long long)img * p.w);
+    HullMergeCtx c;
+    c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
+    c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x;
+    c.rs32 = (unsigned)p.rs; c.wc = p.wc;
+    HullMerge<HullMergeCtx> hm(c, p.L, p.buf_rows);
+    for (int b = p.pb; b < p.nblk; b += p.pb) hm.junction(b * 32);
+}
+
+// A junction only ever touches sites within 2L rows of itself, so junctions >= 4L rows apart can be repaired at
+// the same time: nphase = ceil(4L / run length) launches, launch i takes every nphase-th junction. Any order of
+// repairs ends in the same kind of hull (each pop re-tests both triples around the adjacency it creates).
+// thread = (junction, column).
+__global__ void __launch_bounds__(256) hull_merge_par_kernel(HullParams p) {
+    const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+    const int njun = p.nruns_b - 1;                       // junctions 1 .. njun (junction k is at block k*pb)
+    const int nmine = (njun - p.merge_phase + p.merge_nphase - 1) / p.merge_nphase;  // k = 1 + phase + i*nphase
+    const long long per_img = (long long)nmine * p.w;
+    if (t >= per_img * p.n_img) return;
+    const int img = (int)(t / per_img);
+    const long long r = t - (long long)img * per_img;
+    const int k = 1 + p.merge_phase + p.merge_nphase * (int)(r / p.w), x = (int)(r % p.w);
+    HullMergeCtx c;
+    c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
+    c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x;
+    c.rs32 = (unsigned)p.rs; c.wc = p.wc;
+    HullMerge<HullMergeCtx> hm(c, p.L, p.buf_rows);
+    hm.junction(k * p.pb * 32);
+}
+
+struct HullEmitCtx {
+    const uint32_t* hcol;    // hull word of block 0 of this column
+    const uint8_t* rec_lane;
+    const uint8_t* cls0;
+    const uint8_t* flag0;
+    uint32_t* cring;         // class ring, already offset by lane
+    long long rs;
+    unsigned rs32;
+    int wc, ncg, nrows, nblk, lane;
+    // epilogue (see sweep.cuh)
+    const int32_t* thr;
+    uint8_t* optr;
+    bool store_ok;
+    long long ostride;
+    int qcls, qm, qlo, qhi, qbyte, qsign;
+    const int32_t* qthr;
+
+    __device__ __forceinline__ uint32_t h_ld(int b) const { return b < nblk ? __ldg(hcol + (long long)b * wc) : 0u; }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_lane + (unsigned)r * rs32); }
+    __device__ __forceinline__ uint32_t cls_fetch(int blk) const {
+        int r = blk * 32 + lane;
+        r = r < nrows ? r : nrows - 1;
+        const uint32_t raw = __ldg(reinterpret_cast<const uint32_t*>(cls0 + (long long)r * rs));
+        return warp_transpose32(raw, lane);
+    }
+    __device__ __forceinline__ uint32_t cls_ld(int s) const { return cring[s * 32]; }
+    __device__ __forceinline__ void cls_st(int s, uint32_t v) { cring[s * 32] = v; }
+    __device__ __forceinline__ int q_flag(int blk) const {
+        return (blk < 0 || blk >= nblk) ? 3 : (int)__ldg(flag0 + (long long)blk * ncg);
+    }
+    __device__ __forceinline__ void requant(int cls, int d2c) {
+        if (cls != qcls) {
+            qcls = cls;
+            qthr = thr + cls * 260;
+            qsign = cls ? 1 : -1;
+            qm = level_of(qthr, d2c);
+        } else {
+            while (d2c >= qthr[qm + 1]) ++qm;
+            while (d2c < qthr[qm]) --qm;
+        }
+        qlo = qthr[qm];
+        qhi = qthr[qm + 1];
+        qbyte = cls ? qm : 255 - qm;
+    }
+    __device__ __forceinline__ void out(int cls, int d2c) {
+        const int step = (d2c >= qhi ? 1 : 0) - (d2c < qlo ? 1 : 0);
+        if (step != 0) {
+            qm += step;
+            qbyte += step * qsign;
+            qlo = qthr[qm];
+            qhi = qthr[qm + 1];
+        }
+        if (CQ_UNLIKELY(d2c >= qhi || d2c < qlo || cls != qcls)) requant(cls, d2c);
+        if (store_ok) *optr = (uint8_t)qbyte;
+        optr += ostride;
+    }
+    __device__ __forceinline__ void out_run(int cls, int d2c, int n) {
+        out(cls, d2c);
+        const uint8_t b = (uint8_t)qbyte;
+        for (int i = 1; i < n; ++i) {
+            if (store_ok) *optr = b;
+            optr += ostride;
+        }
+    }
+};
+
+__global__ void __launch_bounds__(kHullWarps * 32) hull_emit_kernel(HullParams p) {
+    extern __shared__ __align__(16) uint8_t s_hull[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int32_t* s_thr = reinterpret_cast<int32_t*>(s_hull);
+    for (int i = threadIdx.x; i < 2 * 260; i += kHullWarps * 32) s_thr[i] = (&p.table->thr[0][0])[i];
+    __syncthreads();
+    long long id = blockIdx.x;
+    const int run = (int)(id % p.nruns_e); id /= p.nruns_e;
+    const int strip = (int)(id % p.nstrips);
+    const int img = (int)(id / p.nstrips);
+    const int cg = strip * kHullWarps + warp;
+    if (cg >= p.ncg) return;
+    // runs are cut at multiples of 32 buffer rows so that whole blocks can be written at once
+    const int bfirst = p.out_begin >> 5;
+    int y0 = (bfirst + run * p.eb) * 32, y1 = y0 + p.eb * 32;
+    y0 = y0 > p.out_begin ? y0 : p.out_begin;
+    y1 = y1 < p.out_end ? y1 : p.out_end;
+    if (y0 >= y1) return;
+    HullEmitCtx c;
+    const int x = cg * 32 + lane;
+    c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
+    const uint8_t* recbase = p.inter + (long long)img * p.buf_rows * p.rs;
+    c.rec_lane = recbase + x; c.cls0 = recbase + p.wp + cg * 4;
+    c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
+    c.cring = reinterpret_cast<uint32_t*>(s_hull + kSweepTableBytes + (size_t)warp * kClsRing * 128) + lane;
+    c.rs = p.rs; c.rs32 = (unsigned)p.rs; c.wc = p.wc; c.ncg = p.ncg; c.nrows = p.buf_rows; c.nblk = p.nblk; c.lane = lane;
+    c.thr = s_thr; c.ostride = p.w; c.store_ok = x < p.w;
+    const int out_rows = p.out_end - p.out_begin;
+    c.optr = p.out + ((long long)img * out_rows + (y0 - p.out_begin)) * (long long)p.w + (x < p.w ? x : 0);
+    c.qcls = -1; c.qm = 1; c.qlo = 0; c.qhi = 0x7fffffff; c.qbyte = 0; c.qsign = 1; c.qthr = s_thr;
+    int lag = p.L;
+    asm volatile("" : "+r"(lag));
+    HullEmit<HullEmitCtx> he(c, lag, p.c2);
+    he.run(y0, y1);
+}
+
+}  // namespace chaq

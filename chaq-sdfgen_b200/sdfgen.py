@@ -224,7 +224,7 @@ def exchange_halos(inter, h, world, rank, spread, group=None):
 
 
 def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, group=None, state=None, stride=1, offset=0,
-                   test_above=True):
+                   test_above=True, events=None):
     """One image of h rows sharded by row bands over `world` ranks (one process per GPU). d_band holds this
     rank's rows. Pass 1 is local; pass 2 needs `spread` rows of the 16-bit intermediate from each neighbour
     band, exchanged point to point (NCCL over NVLink); then pass 2 is local. Returns this rank's output rows.
@@ -245,9 +245,17 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
         nb = int(lib().chaqsdf_envelope_workspace_bytes(w, buf_rows, spread))
         state["ws"] = _workspace(nb, dev) if nb else None
     inter, out = state["inter"], state["out"]
+    if events:
+        events[0].record()
     rowscan_device(d_band, w, rows, spread, inter[halo_top:halo_top + rows], stride=stride, offset=offset,
                    test_above=test_above)
+    if events:
+        events[1].record()
     if world > 1:
         exchange_halos(inter, h, world, rank, spread, group)
+    if events:
+        events[2].record()
     envelope_device(inter, w, buf_rows, halo_top, halo_top + rows, spread, asymmetric, out, workspace=state["ws"])
+    if events:
+        events[3].record()
     return out

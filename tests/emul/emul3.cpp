@@ -1,0 +1,138 @@
+// Host emulation of the build / merge / emit organisation of the banded column pass (hull_core.h) and the level
+// tables (tables.h): the SAME headers the CUDA kernels compile, driven column by column on the CPU, so the logic
+// (piece boundaries, junction repair, cursor walk, quiet blocks) can be checked against the oracle without a GPU.
+// Test infrastructure only; not part of the product library.
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "../../chaq-sdfgen_b200/csrc/tables.h"
+#include "../../chaq-sdfgen_b200/csrc/hull_core.h"
+
+using namespace chaq;
+
+static void rowscan_naive(const uint8_t* mask, int w, int h, int C, std::vector<uint8_t>& g8) {
+    g8.resize((size_t)w * h);
+    for (int y = 0; y < h; ++y) {
+        const uint8_t* m = mask + (size_t)y * w;
+        for (int x = 0; x < w; ++x) {
+            int best = C;
+            for (int d = 1; d < C; ++d) {
+                bool hit = (x - d >= 0 && m[x - d] != m[x]) || (x + d < w && m[x + d] != m[x]);
+                if (hit) { best = d; break; }
+            }
+            g8[(size_t)y * w + x] = (uint8_t)(best - 1);
+        }
+    }
+}
+
+struct Col {
+    const uint8_t* g; const uint8_t* m; size_t stride; int nrows, nblk;
+    std::vector<uint32_t>* H;   // hull words of this column
+    std::vector<uint8_t>* Q;    // block flags of this column (the "group" is this one column)
+    long oob = 0;
+    uint32_t g_row(int r) { if (r < 0 || r >= nrows) { ++oob; return 255; } return g[(size_t)r * stride]; }
+};
+
+struct BuildCtx : Col {
+    int cur = 0, b0 = 0;
+    std::vector<uint32_t> bits;
+    void block_begin(int blk) { cur = blk; }
+    bool block_quiet(int L) {
+        for (int j = 0; j < 32; ++j) { int r = cur * 32 + j; if (r < nrows && g[(size_t)r * stride] < L) return false; }
+        return true;
+    }
+    uint32_t g_push(int j) { return g_row(cur * 32 + j); }
+    uint32_t bits_ld(int i) { if (i < 0 || i >= (int)bits.size()) { ++oob; return 0; } return bits[i]; }
+    void bits_st(int i, uint32_t v) { if (i < 0 || i >= (int)bits.size()) { ++oob; return; } bits[i] = v; }
+    void block_end(int blk, uint32_t word) {
+        int c0 = 1, c1 = 1;
+        for (int j = 0; j < 32; ++j) { int r = blk * 32 + j; if (r >= nrows) r = nrows - 1; if (m[(size_t)r * stride] & 1) c0 = 0; else c1 = 0; }
+        (*Q)[blk] = word ? 2 : (c0 ? 0 : (c1 ? 1 : 2));
+    }
+};
+
+struct MergeCtx : Col {
+    uint32_t h_ld(int b) { if (b < 0 || b >= nblk) { ++oob; return 0; } return (*H)[b]; }
+    void h_st(int b, uint32_t v) { if (b < 0 || b >= nblk) { ++oob; return; } (*H)[b] = v; }
+};
+
+struct EmitCtx : Col {
+    uint32_t ring[kClsRing]; int ring_blk[kClsRing];
+    int* d2; uint8_t* ocls; int nout = 0;
+    uint32_t h_ld(int b) { if (b < 0) { ++oob; return 0; } return b < nblk ? (*H)[b] : 0u; }
+    uint32_t cls_fetch(int blk) {
+        uint32_t wd = 0;
+        if (blk < 0) { ++oob; return 0; }
+        for (int j = 0; j < 32; ++j) { int r = blk * 32 + j; if (r >= nrows) r = nrows - 1; wd |= (uint32_t)(m[(size_t)r * stride] & 1) << j; }
+        return wd;
+    }
+    uint32_t cls_ld(int s) { return ring[s]; }
+    void cls_st(int s, uint32_t v) { ring[s] = v; }
+    int q_flag(int blk) { return (blk < 0 || blk >= nblk) ? 3 : (*Q)[blk]; }
+    void out(int c, int v) { d2[nout] = v; ocls[nout] = (uint8_t)c; ++nout; }
+    void out_run(int c, int v, int n) { for (int i = 0; i < n; ++i) out(c, v); }
+};
+
+// mask: h*w bytes of 0/1. build_blocks: blocks per build run; emit_rows: rows per emit run (0 = whole column);
+// y_begin/y_end: output row range (context rows outside it still exist, as in a row-band buffer).
+// merge_order 0: junctions top to bottom; 1: in nphase = ceil(4L / run length) rounds, round i taking every
+// nphase-th junction (what the parallel merge kernel amounts to: same-round junctions cannot interact).
+extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int asym, int build_blocks, int emit_rows,
+                         int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order) {
+    QuantTable q; build_quant_table(spread, asym, &q);
+    LevelTable lt; build_level_table(q, &lt);
+    const int C = lt.cap_eff, L = C - 1;
+    if (cap_eff) *cap_eff = C;
+    if (C > 256) return 1;
+    if (build_blocks < 1 || build_blocks > kHullMaxPieceBlocks) return 3;
+    std::vector<uint8_t> g8;
+    rowscan_naive(mask, w, h, C, g8);
+    const int nblk = (h + 31) / 32;
+    if (emit_rows <= 0) emit_rows = h;
+    std::vector<int> cd2(h); std::vector<uint8_t> ccls(h);
+    for (int x = 0; x < w; ++x) {
+        std::vector<uint32_t> H(nblk, 0xdeadbeefu);
+        std::vector<uint8_t> Q(nblk, 2);
+        for (int b0 = 0; b0 < nblk; b0 += build_blocks) {
+            BuildCtx c;
+            c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
+            const int b1 = b0 + build_blocks < nblk ? b0 + build_blocks : nblk;
+            c.b0 = b0; c.bits.assign(b1 - b0, 0xdeadbeefu);
+            HullBuild<BuildCtx> hb(c, L);
+            hb.run(b0, b1, h);
+            for (int b = b0; b < b1; ++b) H[b] = c.bits[b - b0];
+            if (c.oob) return 1000;
+        }
+        {
+            MergeCtx c;
+            c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
+            HullMerge<MergeCtx> hm(c, L, h);
+            if (merge_order == 1) {
+                int nphase = (4 * L + build_blocks * 32 - 1) / (build_blocks * 32);
+                if (nphase < 1) nphase = 1;
+                for (int phase = 0; phase < nphase; ++phase)
+                    for (int k = 1 + phase; k * build_blocks < nblk; k += nphase) hm.junction(k * build_blocks * 32);
+            } else {
+                for (int b0 = build_blocks; b0 < nblk; b0 += build_blocks) hm.junction(b0 * 32);
+            }
+            if (c.oob) return 2000;
+        }
+        for (int y0 = y_begin; y0 < y_end; y0 += emit_rows) {
+            const int y1 = y0 + emit_rows < y_end ? y0 + emit_rows : y_end;
+            EmitCtx c;
+            c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
+            c.d2 = cd2.data() + y0; c.ocls = ccls.data() + y0;
+            HullEmit<EmitCtx> he(c, L, lt.c2);
+            he.run(y0, y1);
+            if (c.nout != y1 - y0) return 2;
+            if (c.oob) return 3000;
+        }
+        for (int y = y_begin; y < y_end; ++y) {
+            const int cls = ccls[y];
+            const int mlev = level_of(lt.thr[cls], cd2[y]);
+            out[(size_t)y * w + x] = (uint8_t)(cls ? mlev : 255 - mlev);
+        }
+    }
+    return 0;
+}

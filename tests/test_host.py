@@ -265,6 +265,75 @@ def test_banded_sweep_discs_noise_and_cap(emul2, oracle):
         assert np.array_equal(got, oracle.sdf(tall * 255, 9, 700, spread=256, asymmetric=asym))
 
 
+# ---------------------------------------------------------------- build / merge / emit (hull_core.h), host emulation
+@pytest.fixture(scope="session")
+def emul3(tmp_path_factory):
+    so = str(tmp_path_factory.mktemp("emul3") / "libemul3.so")
+    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-o", so,
+                    os.path.join(ROOT, "tests", "emul", "emul3.cpp")], check=True)
+    L = C.CDLL(so)
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
+    L.emul3_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p,
+                            C.POINTER(C.c_int), C.c_int]
+    return L
+
+
+def _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0=0, y1=None, order=None):
+    """order None: both junction orders (top to bottom; odd then even) must give the same bytes."""
+    if order is None:
+        a, ce = _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0, y1, 0)
+        b, _ = _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0, y1, 1)
+        assert np.array_equal(a, b), "junction orders disagree"
+        return a, ce
+    h, w = mask.shape
+    y1 = h if y1 is None else y1
+    out = np.zeros((h, w), np.uint8)
+    ce = C.c_int()
+    rc = L.emul3_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), build_blocks, emit_rows, y0, y1, out, C.byref(ce),
+                     order)
+    assert rc == 0, f"emulated build/merge/emit failed (rc={rc}: 1 = cap_eff > 256, 2 = row count, >=1000 = out-of-range access)"
+    return out, ce.value
+
+
+def test_hull_build_merge_emit_matches_oracle_random(emul3, oracle):
+    """Run lengths from one block (a junction every 32 rows, far shorter than the reach) to 32 blocks."""
+    rng = np.random.default_rng(5)
+    for it in range(100):
+        h, w = int(rng.integers(1, 400)), int(rng.integers(1, 24))
+        dens = rng.choice([0.0, 0.01, 0.05, 0.3, 0.5, 0.9, 1.0])
+        mask = (rng.random((h, w)) < dens).astype(np.uint8)
+        if it % 3 == 0:
+            yy, xx = np.mgrid[0:h, 0:w]
+            mask = np.zeros((h, w), np.uint8)
+            for _ in range(3):
+                cy, cx, r = rng.integers(0, h), rng.integers(0, w), rng.integers(1, 60)
+                mask |= ((yy - cy) ** 2 + (xx - cx) ** 2 <= r * r).astype(np.uint8)
+        img = (mask * 255).astype(np.uint8)
+        for spread in (1, 2, 5, 16, 40, 100, 256):
+            asym = bool(it & 1)
+            want = oracle.sdf(img, w, h, spread=spread, asymmetric=asym)
+            for bb, er in ((1, 0), (2, 7), (3, 33), (8, 64), (32, 100)):
+                got, _ = _emul3_u8(emul3, mask, spread, asym, bb, er)
+                assert np.array_equal(got, want), (it, h, w, spread, bb, er)
+
+
+def test_hull_discs_noise_and_row_ranges(emul3, oracle):
+    for n, spread, bb, er in ((384, 16, 2, 0), (384, 64, 4, 100), (1024, 256, 16, 400), (1024, 256, 1, 37), (700, 100, 3, 64), (1024, 33, 3, 50), (1024, 15, 1, 0)):
+        img = oracle.syn_discs(n)
+        got, ce = _emul3_u8(emul3, (img > 127).astype(np.uint8), spread, False, bb, er)
+        assert ce <= min(spread + 1, 256)
+        assert np.array_equal(got, oracle.sdf(img, n, n, spread=spread)), (n, spread, bb, er)
+    noise = oracle.syn_noise(300)
+    for spread in (3, 8, 50, 256):
+        got, _ = _emul3_u8(emul3, (noise > 127).astype(np.uint8), spread, True, 2, 50)
+        assert np.array_equal(got, oracle.sdf(noise, 300, 300, spread=spread, asymmetric=True)), spread
+    # a row band of a larger buffer (unaligned ends), as the multi-GPU and pipelined callers use it
+    img = oracle.syn_discs(512)
+    want = oracle.sdf(img, 512, 512, spread=40)
+    got, _ = _emul3_u8(emul3, (img > 127).astype(np.uint8), 40, False, 4, 96, 100, 333)
+    assert np.array_equal(got[100:333], want[100:333])
+
+
 # ---------------------------------------------------------------- chaq_sdfgen command line (reference sdfgen.c:122-244)
 CLI = os.path.join(ROOT, "chaq-sdfgen_b200", "bin", "chaq_sdfgen")
 
