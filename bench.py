@@ -25,8 +25,9 @@ sys.path.insert(0, ROOT)
 
 SIDE = int(os.environ.get("CHAQ_BENCH_SIDE", 16384))
 SPREAD = int(os.environ.get("CHAQ_BENCH_SPREAD", 256))
-# dram__bytes_read+write of one pass-2 launch from the committed ncu --set full capture (profiles/), or None
-TRAFFIC_PASS2 = None
+# dram__bytes_read.sum + dram__bytes_write.sum of one hull_emit_kernel launch from the committed ncu --set full
+# capture (profiles/r01_v5_ncu_summary.txt), bytes
+TRAFFIC_EMIT = 375930112
 WORKLOAD = f"config4: SYN-DISCS({SIDE}) {SIDE}x{SIDE} u8 mask, spread {SPREAD}, symmetric"
 # algorithmic bytes: pass 1 reads the 1 B/px mask and writes the intermediate; pass 2 reads the
 # intermediate and writes the 1 B/px bitmap. The intermediate is 1 B/px of row distance + 1 bit/px of class
@@ -203,6 +204,8 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         sampler.start()
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3 if world == 1 else 4)] for _ in range(K)]
+    if world == 1:
+        pkg.profile_enable(True)  # the library's own CUDA events around the kernels of pass 2, on this stream
     l0 = pkg.launch_count()
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -212,6 +215,10 @@ def run_ours(args, rank, world, local_rank):
     t_end.record()
     barrier()
     launches = pkg.launch_count() - l0
+    kernel_ms = None
+    if world == 1:
+        kernel_ms = pkg.profile_mean_ms()  # mean over the timed steps (first 64)
+        pkg.profile_enable(False)
     clocks = sampler.stop() if rank == 0 else None
     ms_total = t_start.elapsed_time(t_end)
     phases = None
@@ -263,14 +270,21 @@ def run_ours(args, rank, world, local_rank):
     if world == 1:
         p1 = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
         p2 = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
-        pass_bytes = h * w + h * pkg.inter_row_bytes(w, SPREAD)  # the same for both passes
-        a2 = pass_bytes / (p2 * 1e-3) / 1e9
-        a1 = pass_bytes / (p1 * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": "sweep_kernel (pass 2: column envelope + epilogue)", "achieved": a2,
-                    "peak": peak, "unit": "GB/s", "frac": a2 / peak, "traffic": TRAFFIC_PASS2, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": pass_bytes, "ms_per_launch": p2}
-        passes = {"rowscan8_kernel": {"ms": p1, "GB/s": a1, "frac": a1 / peak, "algorithmic_bytes": pass_bytes},
-                  "sweep_kernel": {"ms": p2, "GB/s": a2, "frac": a2 / peak, "algorithmic_bytes": pass_bytes}}
+        inter_bytes = h * pkg.inter_row_bytes(w, SPREAD)
+        hull_bytes = h * w // 8  # the hull bitmask: 1 bit per pixel, written by build, read by emit
+        # algorithmic bytes per launch
+        bytes_of = {"rowscan8_kernel": h * w + inter_bytes, "hull_build_kernel": inter_bytes + hull_bytes,
+                    "hull_merge_par_kernel": 0, "hull_emit_kernel": inter_bytes + hull_bytes + h * w}
+        ms_of = {"rowscan8_kernel": p1, **{k: v for k, v in kernel_ms.items() if k != "calls"}}
+        passes = {k: {"ms": ms_of[k], "GB/s": bytes_of[k] / (ms_of[k] * 1e-3) / 1e9 if bytes_of[k] else None,
+                      "frac": bytes_of[k] / (ms_of[k] * 1e-3) / 1e9 / peak if bytes_of[k] else None,
+                      "algorithmic_bytes": bytes_of[k]} for k in ms_of}
+        passes["pass2_total"] = {"ms": p2, "note": "build + junction merge (2 launches) + emit, CUDA events around the C-ABI call"}
+        dom = "hull_emit_kernel"
+        roofline = {"bound": "hbm", "kernel": dom + " (pass 2: hull walk + class run + quantise, the longest kernel)",
+                    "achieved": passes[dom]["GB/s"], "peak": peak, "unit": "GB/s", "frac": passes[dom]["frac"],
+                    "traffic": TRAFFIC_EMIT, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_of[dom],
+                    "ms_per_launch": ms_of[dom], "launches_averaged": kernel_ms["calls"]}
     # CPU baseline: the reference's own code on this box's host cores, one bounded sample (N=1 only)
     cpu = None
     try:

@@ -330,6 +330,19 @@ int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_b
     return CHAQSDF_OK;
 }
 
+// optional per-kernel timing (chaqsdf_profile_enable): events around the launches of the banded pass 2
+constexpr int kProfSets = 64;
+bool g_prof_on = false;
+int g_prof_n = 0;  // profiled calls since it was enabled (the first kProfSets are kept)
+cudaEvent_t g_prof_ev[kProfSets][4] = {};
+void prof_mark(int i, cudaStream_t st) {
+    if (!g_prof_on || g_prof_n >= kProfSets) return;
+    cudaEvent_t& e = g_prof_ev[g_prof_n][i];
+    if (!e && cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, st);
+    if (i == 3) ++g_prof_n;
+}
+
 // banded pass 2 as build / merge / emit (hull.cuh)
 int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
                 const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st) {
@@ -344,6 +357,7 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     p.nblk = (int)((buf_rows + 31) / 32);
     p.ncg = (int)((w + 31) / 32); p.wc = p.ncg * 32;
     p.nstrips = (p.ncg + kHullWarps - 1) / kHullWarps; p.n_img = (int)n_img;
+    p.nstrips_e = (p.ncg + kEmitWarps - 1) / kEmitWarps;
     p.out_begin = (int)out_begin; p.out_end = (int)out_end;
     p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2;
     // run lengths: enough CTAs to fill the machine a few times over, runs no longer than 512 rows (build) / 1024 (emit)
@@ -366,11 +380,13 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     if (eb < 1) eb = 1;
     if (eb > nbo) eb = nbo;
     p.eb = (int)eb; p.nruns_e = (nbo + p.eb - 1) / p.eb;
-    const long long gb = strips * p.nruns_b, ge = strips * p.nruns_e;
+    const long long gb = strips * p.nruns_b, ge = (long long)n_img * p.nstrips_e * p.nruns_e;
     if (gb > 0x7fffffffLL || ge > 0x7fffffffLL) return fail(CHAQSDF_ERR_ARG, "too many runs for one grid");
     const size_t smem_b = hull_build_smem(p.pb), smem_e = hull_emit_smem();
+    prof_mark(0, st);
     hull_build_kernel<<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
     CQ_LAUNCHED("hull_build_kernel", gb, smem_b);
+    prof_mark(1, st);
     if (p.nruns_b > 1 && !getenv("CHAQSDF_HULL_SEQ")) {
         const int njun = p.nruns_b - 1;
         int nphase = (4 * p.L + p.pb * 32 - 1) / (p.pb * 32);  // same-launch junctions are >= 4L rows apart
@@ -391,8 +407,10 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
         hull_merge_kernel<<<gm, 256, 0, st>>>(p);
         CQ_LAUNCHED("hull_merge_kernel", gm, 0);
     }
-    hull_emit_kernel<<<(unsigned)ge, kHullWarps * 32, smem_e, st>>>(p);
+    prof_mark(2, st);
+    hull_emit_kernel<<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
     CQ_LAUNCHED("hull_emit_kernel", ge, smem_e);
+    prof_mark(3, st);
     return CHAQSDF_OK;
 }
 
@@ -417,6 +435,21 @@ extern "C" {
 int chaqsdf_version(void) { return 110; }
 const char* chaqsdf_last_error_string(void) { return g_err.c_str(); }
 unsigned long long chaqsdf_launch_count(void) { return g_launches.load(); }
+void chaqsdf_profile_enable(int on) { g_prof_on = on != 0; if (on) g_prof_n = 0; }
+int chaqsdf_profile_mean_ms(float ms[3]) {
+    if (!ms) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (g_prof_n == 0) return fail(CHAQSDF_ERR_ARG, "no profiled call of the banded pass 2 yet");
+    ms[0] = ms[1] = ms[2] = 0.f;
+    for (int k = 0; k < g_prof_n; ++k) {
+        CQ_CUDA(cudaEventSynchronize(g_prof_ev[k][3]));
+        for (int i = 0; i < 3; ++i) {
+            float t = 0.f;
+            CQ_CUDA(cudaEventElapsedTime(&t, g_prof_ev[k][i], g_prof_ev[k][i + 1]));
+            ms[i] += t / (float)g_prof_n;
+        }
+    }
+    return g_prof_n;
+}
 
 size_t chaqsdf_inter_row_bytes(size_t w, size_t spread) {
     if (w == 0 || w > CHAQSDF_MAX_DIM || spread == 0) return 0;

@@ -24,6 +24,10 @@
 namespace chaq {
 
 constexpr int kHullWarps = 4;
+#ifndef CQ_EMIT_WARPS
+#define CQ_EMIT_WARPS 4
+#endif
+constexpr int kEmitWarps = CQ_EMIT_WARPS;  // warps (32-column groups) per CTA of the emit kernel
 
 struct HullParams {
     const uint8_t* inter;    // banded intermediate, [n_img][buf_rows] records
@@ -35,6 +39,7 @@ struct HullParams {
     int wp, w, buf_rows, nblk;
     int wc;                  // ncg * 32
     int ncg, nstrips, n_img;
+    int nstrips_e;           // strips of kEmitWarps column groups (emit kernel)
     int out_begin, out_end;
     int pb;                  // blocks per build run
     int nruns_b;             // build runs per strip
@@ -45,7 +50,7 @@ struct HullParams {
 };
 
 __host__ __device__ inline size_t hull_build_smem(int pb) { return (size_t)kHullWarps * (2 * 1024 + (size_t)pb * 128); }
-__host__ __device__ inline size_t hull_emit_smem() { return kSweepTableBytes + (size_t)kHullWarps * kClsRing * 128; }
+__host__ __device__ inline size_t hull_emit_smem() { return kSweepTableBytes + (size_t)kEmitWarps * kClsRing * 128; }
 
 struct HullBuildCtx {
     const uint8_t* gst;      // staging (2 blocks of 32 rows x 32 bytes), generic pointer at lane 0
@@ -247,17 +252,20 @@ struct HullEmitCtx {
     }
 };
 
-__global__ void __launch_bounds__(kHullWarps * 32) hull_emit_kernel(HullParams p) {
+#ifndef CQ_EMIT_MINB
+#define CQ_EMIT_MINB 9
+#endif
+__global__ void __launch_bounds__(kEmitWarps * 32, CQ_EMIT_MINB) hull_emit_kernel(HullParams p) {
     extern __shared__ __align__(16) uint8_t s_hull[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int32_t* s_thr = reinterpret_cast<int32_t*>(s_hull);
-    for (int i = threadIdx.x; i < 2 * 260; i += kHullWarps * 32) s_thr[i] = (&p.table->thr[0][0])[i];
+    for (int i = threadIdx.x; i < 2 * 260; i += kEmitWarps * 32) s_thr[i] = (&p.table->thr[0][0])[i];
     __syncthreads();
     long long id = blockIdx.x;
     const int run = (int)(id % p.nruns_e); id /= p.nruns_e;
-    const int strip = (int)(id % p.nstrips);
-    const int img = (int)(id / p.nstrips);
-    const int cg = strip * kHullWarps + warp;
+    const int strip = (int)(id % p.nstrips_e);
+    const int img = (int)(id / p.nstrips_e);
+    const int cg = strip * kEmitWarps + warp;
     if (cg >= p.ncg) return;
     // runs are cut at multiples of 32 buffer rows so that whole blocks can be written at once
     const int bfirst = p.out_begin >> 5;

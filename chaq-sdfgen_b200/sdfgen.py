@@ -25,7 +25,8 @@ def build_library(force=False):
     return LIB_PATH
 
 
-SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "dist_transform_2d",
+SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "chaqsdf_profile_enable",
+           "chaqsdf_profile_mean_ms", "dist_transform_2d",
            "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
            "chaqsdf_inter_row_bytes",
@@ -44,6 +45,9 @@ def lib():
     sz, vp, i = C.c_size_t, C.c_void_p, C.c_int
     L.chaqsdf_last_error_string.restype = C.c_char_p
     L.chaqsdf_launch_count.restype = C.c_ulonglong
+    L.chaqsdf_profile_enable.argtypes = [i]
+    L.chaqsdf_profile_enable.restype = None
+    L.chaqsdf_profile_mean_ms.argtypes = [C.POINTER(C.c_float)]
     L.dist_transform_2d.argtypes = [vp, sz, sz]
     L.dist_transform_2d.restype = None
     L.chaqsdf_u8.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp]
@@ -73,6 +77,21 @@ def _check(rc):
 
 def launch_count():
     return int(lib().chaqsdf_launch_count())
+
+
+def profile_enable(on=True):
+    """Bracket the kernels of the banded pass 2 with CUDA events (bench.py's roofline)."""
+    lib().chaqsdf_profile_enable(int(bool(on)))
+
+
+def profile_mean_ms():
+    """{kernel: mean ms} over the profiled calls of the banded pass 2: hull build, junction merge, hull emit."""
+    ms = (C.c_float * 3)()
+    n = lib().chaqsdf_profile_mean_ms(ms)
+    if n <= 0:
+        raise ChaqSdfError(lib().chaqsdf_last_error_string().decode())
+    return {"hull_build_kernel": float(ms[0]), "hull_merge_par_kernel": float(ms[1]), "hull_emit_kernel": float(ms[2]),
+            "calls": int(n)}
 
 
 def _stream_ptr(stream):

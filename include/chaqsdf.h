@@ -42,6 +42,14 @@ const char* chaqsdf_last_error_string(void);
 /* Number of kernels this library has launched in this process (all threads); for bench accounting. */
 unsigned long long chaqsdf_launch_count(void);
 
+/* Per-kernel timing of the banded pass 2 (spread <= 256), for bench.py's roofline: when enabled, the library
+ * brackets its own launches with CUDA events on the caller's stream (the first 64 calls after enabling).
+ * chaqsdf_profile_mean_ms waits for them and returns the mean milliseconds of { hull build, junction merge,
+ * hull emit } and, as its value, the number of calls averaged (0 with an error string if none). Not thread-safe;
+ * leave it off in production (it adds four event records per call). */
+void chaqsdf_profile_enable(int on);
+int chaqsdf_profile_mean_ms(float ms[3]);
+
 /* ---- df.h:6 drop-in -------------------------------------------------------------------------------
  * img: host, row-major float[w*h], in place. Input heights 0 (seed) or +INF (no seed), as the CLI passes
  * (sdfgen.c:281,286); output sqrtf of the exact squared Euclidean distance to the nearest seed, +INF if

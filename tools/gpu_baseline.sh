@@ -9,6 +9,6 @@ python tools/profile_step.py 16384 256 3 > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv \
     python tools/profile_step.py 16384 256 3 > gpurun_out/ncu_launches.log 2>&1
 python tools/profile_step.py 16384 256 2 > gpurun_out/plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:'sweep|rowscan8' -s 2 -c 2 -f -o gpurun_out/prof \
+ncu --set full --clock-control none --import-source on -k regex:'hull|rowscan8' -s 5 -c 5 -f -o gpurun_out/prof \
     python tools/profile_step.py 16384 256 2 > gpurun_out/ncu_full.log 2>&1
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json gpurun_out/bench_ref.json; cat gpurun_out/plain.log; tail -3 gpurun_out/bench.err
