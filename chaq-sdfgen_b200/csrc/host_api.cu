@@ -177,7 +177,7 @@ int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t off
     std::lock_guard<std::mutex> lk(g_pool.mu);
     // large images on the banded path: overlap upload, kernels and download band by band
     if (spread <= 256 && w * h >= ((size_t)1 << 22)) {
-        size_t band = ((size_t)64 << 20) / (w * stride);  // ~64 MB of input per band
+        size_t band = ((size_t)32 << 20) / (w * stride);  // ~32 MB of input per band
         if (const char* e = getenv("CHAQSDF_PIPE_ROWS")) band = (size_t)atoll(e);
         band = (band + 31) & ~(size_t)31;
         if (band < 2 * spread + 64) band = (2 * spread + 64 + 31) & ~(size_t)31;

@@ -29,4 +29,10 @@ for world in (1, 2, 4, 8):
             torch.cuda.synchronize()
             best = min(best, a.elapsed_time(b))
         ts.append(round(best, 3))
-    print(f"world {world}: envelope ms per rank {ts}  max {max(ts)}  sum {sum(ts):.3f}")
+    pkg.profile_enable(True)
+    r0, r1, ht, hb, _, _ = pkg.halo_plan(side, world, world // 2, spread)
+    pkg.envelope_device(inter[r0 - ht:r1 + hb], side, r1 + hb - (r0 - ht), ht, ht + (r1 - r0), spread, False, out[r0:r1], workspace=ws)
+    km = pkg.profile_mean_ms()
+    pkg.profile_enable(False)
+    print(f"world {world}: envelope ms per rank {ts}  max {max(ts)}  sum {sum(ts):.3f}  kernels(rank {world // 2}) " +
+          " ".join(f"{k.split('_')[1]}={v:.3f}" for k, v in km.items() if k != "calls"))
