@@ -220,6 +220,25 @@ def test_config4_full_size(pkg, oracle):
     assert np.array_equal(gt, want.T)
 
 
+def test_pass2_organisations_and_run_lengths_agree(pkg, oracle, monkeypatch):
+    """Pass 2 as build/merge/emit with forced run lengths (junction every 32 rows .. one run per column, parallel
+    and sequential junction repair) and as the single sweep: all must give the oracle's bytes."""
+    rng = np.random.default_rng(77)
+    cases = [(oracle.syn_discs(1536), 1536, 1536, 256), (oracle.syn_discs(1024), 1024, 1024, 40),
+             (oracle.syn_noise(700), 700, 700, 9), (random_shapes(rng, 900, 333), 333, 900, 100)]
+    envs = [{}, {"CHAQSDF_HULL_PB": "1", "CHAQSDF_HULL_EB": "1"}, {"CHAQSDF_HULL_PB": "3", "CHAQSDF_HULL_EB": "5"},
+            {"CHAQSDF_HULL_PB": "32", "CHAQSDF_HULL_EB": "32"}, {"CHAQSDF_HULL_SEQ": "1", "CHAQSDF_HULL_PB": "2"},
+            {"CHAQSDF_PASS2": "sweep"}, {"CHAQSDF_PASS2": "sweep", "CHAQSDF_SWEEP_SPLIT": "rows"}]
+    for img, w, h, spread in cases:
+        want = oracle.sdf(img, w, h, spread=spread)
+        for env in envs:
+            for k in ("CHAQSDF_HULL_PB", "CHAQSDF_HULL_EB", "CHAQSDF_HULL_SEQ", "CHAQSDF_PASS2", "CHAQSDF_SWEEP_SPLIT"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            assert np.array_equal(gpu_u8(pkg, img, w, h, spread=spread), want), (w, h, spread, env)
+
+
 def test_host_api_pipelined_bands(pkg, oracle, monkeypatch):
     """chaqsdf_u8 on a large image goes through in row bands (upload / kernels / download overlapped); the result
     must not depend on the band height, including bands barely taller than the context they need."""
