@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "../../include/chaqsdf.h"
+#include "dt_float.cuh"
 
 namespace chaq {
 int set_error(int code, const char* msg);
@@ -205,6 +206,27 @@ int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t off
     return CHAQSDF_OK;
 }
 
+// General heights (or CHAQSDF_DT2D=stock): the reference's float32 envelope, one thread per line (dt_float.cuh).
+// d_f holds the image on the device; on success it holds the result.
+static int dt2d_float_device(float* d_f, size_t w, size_t h, cudaStream_t st) {
+    const size_t n = w * h;
+    void *d_tmp, *d_v, *d_z;
+    if (pool_get(1, n * sizeof(float), &d_tmp) != cudaSuccess || pool_get(2, n * sizeof(int), &d_v) != cudaSuccess ||
+        pool_get(3, n * sizeof(float), &d_z) != cudaSuccess)
+        return set_error(CHAQSDF_ERR_CUDA, "device allocation failed");
+    chaq::DtFloatParams p;
+    p.v = (int*)d_v; p.z = (float*)d_z;
+    p.in = d_f; p.out = (float*)d_tmp; p.len = (int)w; p.nlines = (int)h; p.do_sqrt = 0;   // df.c:130
+    chaq::dt_float_kernel<<<(unsigned)((h + 127) / 128), 128, 0, st>>>(p);
+    if (cudaGetLastError() != cudaSuccess) return set_error(CHAQSDF_ERR_CUDA, "dt_float_kernel launch failed");
+    chaq::note_launch();
+    p.in = (const float*)d_tmp; p.out = d_f; p.len = (int)h; p.nlines = (int)w; p.do_sqrt = 1;  // df.c:133
+    chaq::dt_float_kernel<<<(unsigned)((w + 127) / 128), 128, 0, st>>>(p);
+    if (cudaGetLastError() != cudaSuccess) return set_error(CHAQSDF_ERR_CUDA, "dt_float_kernel launch failed");
+    chaq::note_launch();
+    return CHAQSDF_OK;
+}
+
 // df.h:6. Status of the last call on this thread is readable through chaqsdf_dt2d_last_status().
 static thread_local int g_dt_status = 0;
 int chaqsdf_dt2d_last_status(void) { return g_dt_status; }
@@ -231,7 +253,17 @@ void dist_transform_2d(float* img, size_t w, size_t h) {
     int flag = 0;
     if (cudaMemcpyAsync(&flag, g_pool.flag, sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess) return;
     if (cudaStreamSynchronize(st) != cudaSuccess) return;
-    if (flag) { g_dt_status = set_error(CHAQSDF_ERR_ARG, "dist_transform_2d: heights other than 0/+INF"); return; }  // heights other than {0,+INF}: untouched
+    const char* mode = getenv("CHAQSDF_DT2D");
+    if (flag || (mode && mode[0] == 's')) {  // sampled function, or stock-compatible float32 output asked for
+        if (w > CHAQSDF_MAX_DIM || h > CHAQSDF_MAX_DIM) { g_dt_status = set_error(CHAQSDF_ERR_ARG, "image side exceeds 32768"); return; }
+        if (n == 1) { g_dt_status = CHAQSDF_OK; return; }  // df.c:32-36: a single cell is returned as it is
+        int rc = dt2d_float_device((float*)d_f, w, h, st);
+        if (rc) { g_dt_status = rc; return; }
+        if (cudaMemcpyAsync(img, d_f, n * sizeof(float), cudaMemcpyDeviceToHost, st) != cudaSuccess) return;
+        if (cudaStreamSynchronize(st) != cudaSuccess) return;
+        g_dt_status = CHAQSDF_OK;
+        return;
+    }
     // seeds are class 1; f_in = distance to the nearest class-1 pixel (0 on the seeds themselves)
     int rc = chaqsdf_fields_device((const uint8_t*)d_mask, w, h, 1, 0, 1, 1, 0, nullptr, nullptr, (float*)d_f, nullptr,
                                    nullptr, nullptr, d_ws, ws_bytes, st);

@@ -51,10 +51,14 @@ void chaqsdf_profile_enable(int on);
 int chaqsdf_profile_mean_ms(float ms[3]);
 
 /* ---- df.h:6 drop-in -------------------------------------------------------------------------------
- * img: host, row-major float[w*h], in place. Input heights 0 (seed) or +INF (no seed), as the CLI passes
- * (sdfgen.c:281,286); output sqrtf of the exact squared Euclidean distance to the nearest seed, +INF if
- * there is none. Thread-safe (called from two OpenMP section threads at sdfgen.c:277-289). Like the
+ * img: host, row-major float[w*h], in place; output sqrtf of the lower envelope min_q |p-q|^2 + img[q], +INF if
+ * no sample is finite. Thread-safe (called from two OpenMP section threads at sdfgen.c:277-289). Like the
  * original it has no return value; on error it leaves img untouched and records the error string.
+ *   heights all 0 / +INF (what the CLI passes, sdfgen.c:281,286): exact integer kernels; identical to the stock
+ *     build wherever that is exact (sides <= 4098), the exact EDT beyond;
+ *   any other height, or CHAQSDF_DT2D=stock in the environment: the reference's float32 envelope restated
+ *     operation by operation (csrc/dt_float.cuh), bit-identical to the stock build on square images of any size,
+ *     including its inexactness beyond side 4098.
  * Works for non-square images (the original does not: df.c:47, df.c:92). */
 void dist_transform_2d(float* img, size_t w, size_t h);
 int chaqsdf_dt2d_last_status(void); /* status of the calling thread's last dist_transform_2d */

@@ -159,10 +159,48 @@ def test_dist_transform_2d_dropin(pkg, oracle, ref):
     f[3, 60] = 0
     got = pkg.dist_transform_2d(f.copy())
     assert np.array_equal(got.view(np.uint32), oracle.dist_transform_2d_binary(f).view(np.uint32))
-    bad = np.ones((8, 8), np.float32)  # general heights: refused, buffer untouched
-    with pytest.raises(pkg.ChaqSdfError):
-        pkg.dist_transform_2d(bad)
-    assert (bad == 1).all()
+
+
+def test_dist_transform_2d_general_heights(pkg, ref, monkeypatch):
+    """Sampled functions (any finite height or +INF) take the float32 path that restates df.c:29-97 operation by
+    operation: bit-identical to the stock OpenMP build on square images (the only shape it is defined for)."""
+    rng = np.random.default_rng(31)
+    for n in (1, 2, 3, 17, 64, 257, 700):
+        for kind in range(4):
+            f = (rng.random((n, n)) * [1.0, 50.0, 4000.0, 1e6][kind]).astype(np.float32)
+            if kind >= 1:
+                f[rng.random((n, n)) < [0, 0.3, 0.9, 0.995][kind]] = np.inf
+            if kind == 2:
+                f[rng.random((n, n)) < 0.05] = -3.5  # negative heights: accepted like the stock build accepts them
+            want = ref.dist_transform_2d(f)
+            got = pkg.dist_transform_2d(f.copy())
+            nan = np.isnan(want)  # sqrtf of a negative envelope value: NaN in both, payload bits are not compared
+            assert np.array_equal(np.isnan(got), nan), (n, kind)
+            assert np.array_equal(got.view(np.uint32)[~nan], want.view(np.uint32)[~nan]), (n, kind)
+    f = np.full((33, 33), np.inf, np.float32)
+    f[5, 7] = 2.25
+    assert np.array_equal(pkg.dist_transform_2d(f.copy()).view(np.uint32), ref.dist_transform_2d(f).view(np.uint32))
+    # non-square: the stock build is undefined there; check against a float64 brute force
+    h, w = 23, 41
+    f = (rng.random((h, w)) * 30).astype(np.float32)
+    f[rng.random((h, w)) < 0.7] = np.inf
+    yy, xx = np.mgrid[0:h, 0:w]
+    fin = np.isfinite(f)
+    cand = ((yy[..., None] - yy[fin]) ** 2 + (xx[..., None] - xx[fin]) ** 2 + f[fin].astype(np.float64))
+    want = np.sqrt(cand.min(axis=-1))
+    got = pkg.dist_transform_2d(f.copy())
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-5)
+    # stock-compatible mode on a binary image beyond side 4098, where the stock float32 envelope is inexact
+    # (SURVEY.md 0.3): same bits as the stock build; the default (exact) mode differs from it there
+    n = 4300
+    seeds = rng.random((n, n)) < 0.00002
+    seeds[0, 0] = True
+    f = np.where(seeds, np.float32(0), np.float32(np.inf)).astype(np.float32)
+    want = ref.dist_transform_2d(f)
+    monkeypatch.setenv("CHAQSDF_DT2D", "stock")
+    got = pkg.dist_transform_2d(f.copy())
+    monkeypatch.delenv("CHAQSDF_DT2D")
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
 
 
 def test_batched_glyphs(pkg, oracle):
