@@ -10,7 +10,10 @@
 //   * output type: -f wins, else the three characters after the last '.' of the output name compared to
 //     png bmp jpg tga, else PNG;  the result is a 1-channel 8-bit image;
 //   * the image is decoded to (luminance, alpha) pairs; the alpha channel is tested unless -l is given.
-// Added: -t prints the time spent in the library call to stderr (the reference ignores unknown flags).
+// Added: -t prints the time spent in the library call to stderr (the reference ignores unknown flags); binary PGM
+// (P5, maxval 255) is read and written directly (input recognised by its magic, output by "-f pgm" or a .pgm
+// name), for images beyond what stb_image can decode -- a PGM has no alpha, so like any image without alpha it is
+// all "inside" unless -l tests its grey values.
 //
 // Image decoding/encoding is stb_image / stb_image_write, compiled from the reference's include directory
 // (they are its third-party submodule; nothing is copied into this repository).
@@ -31,7 +34,7 @@
 
 namespace {
 
-enum class Kind { Unknown, Png, Bmp, Jpg, Tga };
+enum class Kind { Unknown, Png, Bmp, Jpg, Tga, Pgm };
 
 struct Options {
     const char* in = nullptr;
@@ -45,7 +48,7 @@ struct Options {
 
 void print_usage() {
     std::puts("usage: chaq_sdfgen [-f filetype] -i file -o file [-q n] [-s n] [-ahln]\n"
-              "    -f filetype   output type: png, bmp, jpg or tga (default: from the output name, else png)\n"
+              "    -f filetype   output type: png, bmp, jpg, tga (or pgm) (default: from the output name, else png)\n"
               "    -i file       input image; \"-\" reads stdin\n"
               "    -o file       output image; \"-\" writes stdout\n"
               "    -q n          jpeg quality, 1-100 (default 100)\n"
@@ -68,7 +71,7 @@ void print_usage() {
 }
 
 Kind kind_of(const char* s) {
-    static const struct { const char* tag; Kind k; } table[] = {{"png", Kind::Png}, {"bmp", Kind::Bmp}, {"jpg", Kind::Jpg}, {"tga", Kind::Tga}};
+    static const struct { const char* tag; Kind k; } table[] = {{"png", Kind::Png}, {"bmp", Kind::Bmp}, {"jpg", Kind::Jpg}, {"tga", Kind::Tga}, {"pgm", Kind::Pgm}};
     for (const auto& e : table)
         if (std::strncmp(s, e.tag, 3) == 0) return e.k;
     return Kind::Unknown;
@@ -127,6 +130,25 @@ bool parse(int argc, char** argv, Options* o) {
 
 void to_stdout(void*, void* data, int size) { std::fwrite(data, (size_t)size, 1, stdout); }
 
+// binary PGM: "P5" <w> <h> <maxval> <one whitespace> bytes; comments (#...) allowed between header tokens
+bool read_pgm_header(FILE* f, size_t* w, size_t* h) {
+    size_t v[3];
+    for (int i = 0; i < 3; ++i) {
+        int c = std::fgetc(f);
+        while (c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '#') {
+            if (c == '#') while (c != '\n' && c != EOF) c = std::fgetc(f);
+            c = std::fgetc(f);
+        }
+        if (c < '0' || c > '9') return false;
+        size_t x = 0;
+        while (c >= '0' && c <= '9') { x = x * 10 + (size_t)(c - '0'); c = std::fgetc(f); }
+        v[i] = x;
+        if (i == 2 && !(c == ' ' || c == '\t' || c == '\n' || c == '\r')) return false;
+    }
+    *w = v[0]; *h = v[1];
+    return v[2] == 255 && v[0] > 0 && v[1] > 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -134,14 +156,43 @@ int main(int argc, char** argv) {
     if (!parse(argc, argv, &o)) return 0;
 
     int w = 0, h = 0, n = 0;
-    unsigned char* ya = o.from_stdin ? stbi_load_from_file(stdin, &w, &h, &n, 2) : stbi_load(o.in, &w, &h, &n, 2);
-    if (!ya) die(false, "Input file could not be opened.");
+    unsigned char* ya = nullptr;
+    std::vector<unsigned char> grey;  // PGM input: one byte per pixel
+    FILE* fin = o.from_stdin ? stdin : std::fopen(o.in, "rb");
+    if (!fin) die(false, "Input file could not be opened.");
+    const int c0 = std::fgetc(fin), c1 = std::fgetc(fin);
+    if (c0 == 'P' && c1 == '5') {
+        size_t pw = 0, ph = 0;
+        if (!read_pgm_header(fin, &pw, &ph) || pw > 32768 || ph > 32768) die(false, "Input file could not be opened.");
+        grey.resize(pw * ph);
+        if (std::fread(grey.data(), 1, grey.size(), fin) != grey.size()) die(false, "Input file could not be opened.");
+        if (o.channel == 1) std::memset(grey.data(), 255, grey.size());  // no alpha channel: opaque everywhere
+        w = (int)pw; h = (int)ph;
+    } else {
+        if (c1 != EOF) std::ungetc(c1, fin);
+        if (c0 != EOF) std::ungetc(c0, fin);  // two pushed-back bytes: fine for files; for pipes see below
+        if (o.from_stdin) {
+            // stdin may not take back two bytes: hand stb the whole stream from memory instead
+            std::vector<unsigned char> all;
+            unsigned char buf[1 << 16];
+            size_t got;
+            while ((got = std::fread(buf, 1, sizeof buf, fin)) > 0) all.insert(all.end(), buf, buf + got);
+            ya = stbi_load_from_memory(all.data(), (int)all.size(), &w, &h, &n, 2);
+        } else {
+            std::fclose(fin);
+            fin = nullptr;
+            ya = stbi_load(o.in, &w, &h, &n, 2);
+        }
+        if (!ya) die(false, "Input file could not be opened.");
+    }
+    if (fin && fin != stdin) std::fclose(fin);
 
     std::vector<unsigned char> sdf((size_t)w * (size_t)h);
     const auto t0 = std::chrono::steady_clock::now();
-    const int rc = chaqsdf_u8(ya, (size_t)w, (size_t)h, 2, o.channel, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, sdf.data());
+    const int rc = ya ? chaqsdf_u8(ya, (size_t)w, (size_t)h, 2, o.channel, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, sdf.data())
+                      : chaqsdf_u8(grey.data(), (size_t)w, (size_t)h, 1, 0, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, sdf.data());
     const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-    stbi_image_free(ya);
+    if (ya) stbi_image_free(ya);
     if (rc != CHAQSDF_OK) die(false, "distance field failed (%d): %s", rc, chaqsdf_last_error_string());
     if (o.timing) std::fprintf(stderr, "chaqsdf_u8: %dx%d spread %zu in %.3f ms (%.1f Mpix/s, host buffers)\n", w, h, o.spread, ms, w * (double)h / ms / 1e3);
 
@@ -157,6 +208,15 @@ int main(int argc, char** argv) {
             ok = o.to_stdout ? stbi_write_jpg_to_func(to_stdout, nullptr, w, h, 1, sdf.data(), (int)o.quality)
                              : stbi_write_jpg(o.out, w, h, 1, sdf.data(), (int)o.quality);
             break;
+        case Kind::Pgm: {
+            FILE* fo = o.to_stdout ? stdout : std::fopen(o.out, "wb");
+            if (fo) {
+                std::fprintf(fo, "P5\n%d %d\n255\n", w, h);
+                ok = std::fwrite(sdf.data(), 1, sdf.size(), fo) == sdf.size();
+                if (fo != stdout) std::fclose(fo);
+            }
+            break;
+        }
         case Kind::Tga:
             ok = o.to_stdout ? stbi_write_tga_to_func(to_stdout, nullptr, w, h, 1, sdf.data()) : stbi_write_tga(o.out, w, h, 1, sdf.data());
             break;

@@ -340,3 +340,30 @@ def test_cli_golden_pair_and_flags(pkg, oracle, tmp_path):
         assert r.returncode == 0, r.stderr
         want = oracle.sdf(np.ascontiguousarray(img), 130, 90, spread=12, test_above=above, asymmetric="-a" in flags)
         assert np.array_equal(np.asarray(Image.open(dst)), want), flags
+
+
+def test_cli_pgm_passthrough(pkg, oracle, tmp_path):
+    """Binary PGM in and out (for images beyond stb_image's reach): header with a comment, luminance test, stdin."""
+    import subprocess
+    cli = os.path.join(ROOT, "chaq-sdfgen_b200", "bin", "chaq_sdfgen")
+    if not os.path.exists(cli):
+        pytest.skip("bin/chaq_sdfgen not built")
+    w, h, spread = 300, 170, 21
+    img = oracle.syn_discs(w, h)
+    src, dst = tmp_path / "in.pgm", tmp_path / "out.pgm"
+    src.write_bytes(b"P5\n# made by a test\n%d %d\n255\n" % (w, h) + img.tobytes())
+    want = oracle.sdf(img, w, h, spread=spread)
+
+    def body(raw):
+        assert raw.startswith(b"P5\n%d %d\n255\n" % (w, h))
+        return np.frombuffer(raw[len(b"P5\n%d %d\n255\n" % (w, h)):], np.uint8).reshape(h, w)
+
+    r = subprocess.run([cli, "-i", str(src), "-o", str(dst), "-s", str(spread), "-l"], capture_output=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert np.array_equal(body(dst.read_bytes()), want)
+    r = subprocess.run([cli, "-i", "-", "-o", "-", "-f", "pgm", "-s", str(spread), "-l"], input=src.read_bytes(),
+                       capture_output=True, timeout=120)
+    assert r.returncode == 0 and np.array_equal(body(r.stdout), want)
+    # no alpha channel in a PGM: the default (alpha) test sees an opaque image -> all inside -> all 255
+    r = subprocess.run([cli, "-i", str(src), "-o", str(dst), "-s", str(spread)], capture_output=True, timeout=120)
+    assert r.returncode == 0 and (body(dst.read_bytes()) == 255).all()
