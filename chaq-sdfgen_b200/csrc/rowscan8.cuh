@@ -24,7 +24,13 @@
 
 namespace chaq {
 
-constexpr int kRow8Warps = 8;
+#ifndef CQ_ROW8_WARPS
+#define CQ_ROW8_WARPS 8
+#endif
+#ifndef CQ_ROW8_MINB
+#define CQ_ROW8_MINB 4
+#endif
+constexpr int kRow8Warps = CQ_ROW8_WARPS;
 
 struct RowScan8Params {
     const uint8_t* img;
@@ -40,7 +46,7 @@ struct RowScan8Params {
     int nstrips;         // 128-column strips = wp/128; busy bytes live at record offset wp + wp/8
 };
 
-__global__ void __launch_bounds__(kRow8Warps * 32) rowscan8_kernel(RowScan8Params p) {
+__global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel(RowScan8Params p) {
     extern __shared__ uint32_t s_bits8[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long row = (long long)blockIdx.x * kRow8Warps + warp;
