@@ -55,7 +55,8 @@ __global__ void __launch_bounds__(kRowWarps * 32) rowscan_kernel(RowScanParams p
     if (p.stride == 1 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
         const int nfull = w >> 9;  // chunks of 512 pixels: 16 per lane
         const uint4* s4 = reinterpret_cast<const uint4*>(src);
-        for (int i = 0; i < nfull; ++i) {
+#pragma unroll 8
+        for (int i = 0; i < nfull; ++i) {  // eight loads in flight per warp: the loop is load-latency bound otherwise
             uint4 q = __ldg(s4 + (size_t)i * 32 + lane);
             uint32_t m = class_nibble(q.x, above) | (class_nibble(q.y, above) << 4) |
                          (class_nibble(q.z, above) << 8) | (class_nibble(q.w, above) << 12);

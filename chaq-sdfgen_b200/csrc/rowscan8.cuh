@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel
         const int nfull = w >> 9;  // chunks of 512 pixels: 16 per lane
         const uint4* s4 = reinterpret_cast<const uint4*>(src);
 #pragma unroll 8
-        for (int i = 0; i < nfull; ++i) {  // unrolled: four 512-byte loads of the warp in flight, the pass is latency-bound
+        for (int i = 0; i < nfull; ++i) {  // unrolled: eight 512-byte loads of the warp in flight; the pass is load-latency bound otherwise
             uint4 q = __ldg(s4 + (size_t)i * 32 + lane);
             uint32_t m = class_nibble(q.x, above) | (class_nibble(q.y, above) << 4) |
                          (class_nibble(q.z, above) << 8) | (class_nibble(q.w, above) << 12);
