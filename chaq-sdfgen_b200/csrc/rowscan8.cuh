@@ -70,6 +70,21 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel
             if (!(lane & 1)) bits[i * 16 + (lane >> 1)] = m | (o << 16);
         }
         word0 = nfull * 16;
+        if ((w & 15) == 0 && (w & 511) != 0) {
+            // the rest of the row (or the whole of a narrow one, e.g. a 256-pixel glyph) as one partial 512-pixel
+            // chunk: lanes whose 16 pixels lie inside the row load them, the others contribute no bits
+            const int x = nfull * 512 + lane * 16;
+            uint32_t m = 0u;
+            if (x < w) {
+                const uint4 q = __ldg(s4 + (size_t)nfull * 32 + lane);
+                m = class_nibble(q.x, above) | (class_nibble(q.y, above) << 4) | (class_nibble(q.z, above) << 8) |
+                    (class_nibble(q.w, above) << 12);
+            }
+            const uint32_t o = __shfl_xor_sync(0xffffffffu, m, 1);
+            const int wi = nfull * 16 + (lane >> 1);
+            if (!(lane & 1) && wi < p.nwords) bits[wi] = m | (o << 16);
+            word0 = p.nwords;
+        }
     }
     for (int wi = word0; wi < p.nwords; ++wi) {
         int x = wi * 32 + lane;

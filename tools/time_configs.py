@@ -41,7 +41,13 @@ if "c3" in which:
     ws = torch.empty(pkg.workspace_bytes(n, n, s, g), dtype=torch.uint8, device="cuda")
     out = torch.empty((g, n, n), dtype=torch.uint8, device="cuda")
     ms = timed(lambda: pkg.sdf_u8_batched_device(d, g, n, n, spread=s, out=out, workspace=ws))
-    print(f"C3 4096 x 256^2 s16: {ms:.3f} ms  {g*n*n/ms/1e3:.0f} Mpix/s")
+    pkg.profile_enable(True)
+    pkg.sdf_u8_batched_device(d, g, n, n, spread=s, out=out, workspace=ws)
+    km = pkg.profile_mean_ms()
+    pkg.profile_enable(False)
+    k2 = sum(v for k, v in km.items() if k != "calls")
+    print(f"C3 4096 x 256^2 s16: {ms:.3f} ms  {g*n*n/ms/1e3:.0f} Mpix/s   pass 2 kernels " +
+          " ".join(f"{k.split('_')[1]}={v:.3f}" for k, v in km.items() if k != "calls") + f"  -> pass 1 ~{ms - k2:.3f} ms")
 if "c5" in which:
     for n, s in ((16384, 1024), (32768, 1024)):
         try:
