@@ -210,6 +210,7 @@ struct HullEmit {
     int eblk;       // cursor: the sites after nxt (after cur if there is no nxt) are the bits of ehw in block eblk,
     uint32_t ehw;   // then the blocks after eblk
     int n0, n1, n2; // blocks of the quiet window with flag 0 / 1 / 2
+    int ev;         // see set_ev
 
     CQ_HD HullEmit(Ctx& ctx, int lag, int c2) : c(ctx), L(lag), C2(c2), reach((lag + 31) / 32) {}
 
@@ -242,7 +243,7 @@ struct HullEmit {
         lastknown = blk * 32 + 31;
         if (nb == kFarRow) {
             const uint32_t x = w ^ (ecls ? 0xFFFFFFFFu : 0u);
-            if (x) nb = blk * 32 + cq_lowbit(x);
+            if (x) { nb = blk * 32 + cq_lowbit(x); ev = cq_min(ev, nb); }
         }
     }
     CQ_HD int height(int r) {
@@ -264,6 +265,15 @@ struct HullEmit {
             ehw = c.h_ld(eblk);
         }
     }
+    // ev = the first row at which something other than the plain walk has to happen: the class run ends (nb), the
+    // current site drops out of reach (cur_p + L + 1), or the successor has to be looked up again because a new
+    // block of the hull has come within reach. One compare per row replaces three.
+    CQ_HD void set_ev(int er) {
+        int t = nb;
+        if (cur_p >= 0) t = cq_min(t, cur_p + L + 1);
+        if (nxt_p < 0) t = cq_min(t, ehw != 0u ? er : (eblk + 1) * 32 - L);
+        ev = t;
+    }
     CQ_HD int advance(int er, int fn) {
         int fc;
         do {
@@ -272,18 +282,23 @@ struct HullEmit {
             const int dn = er - nxt_p;
             fn = dn * dn + nxt_h;
         } while (fn <= fc);
+        set_ev(er + 1);
         return fc;
     }
-    CQ_HD void emit(int er) {
-        ++upd;
-        if (CQ_UNLIKELY(er == nb)) class_flip(er);
+    CQ_HD void housekeeping(int er) {
+        if (er == nb) class_flip(er);
         if (nxt_p < 0 && (ehw != 0u || (eblk + 1) * 32 <= er + L)) next_site(er + L);
         // a site more than L rows above er no longer matters: move on to the first one within reach
         const int lowrow = cq_max(er - L, 0);
-        while (CQ_UNLIKELY((unsigned)cur_p < (unsigned)lowrow)) {
+        while ((unsigned)cur_p < (unsigned)lowrow) {
             cur_p = nxt_p; cur_h = nxt_p < 0 ? kNoCurH : nxt_h;
             if (nxt_p >= 0) next_site(er + L);
         }
+        set_ev(er + 1);
+    }
+    CQ_HD void emit(int er) {
+        ++upd;
+        if (CQ_UNLIKELY(er >= ev)) housekeeping(er);
         const int d = er - cur_p;
         int fc = d * d + cur_h;
         const int dn = er - nxt_p;
@@ -323,6 +338,7 @@ struct HullEmit {
             eblk = s >> 5;
             ehw = c.h_ld(eblk) & (0xFFFFFFFFu << (s & 31));
         }
+        set_ev(y0);
         // quiet window of block B: blocks B-reach .. B+reach
         n0 = n1 = n2 = 0;
         for (int b = B0 - reach; b <= B0 + reach; ++b) q_add(b, 1);
@@ -336,7 +352,7 @@ struct HullEmit {
             if (r1 - r0 == 32 && n2 == 0 && (n0 == 0 || n1 == 0)) {
                 // no site and no class change within reach of any of the 32 rows, in any column of the group
                 ++upd;
-                if (CQ_UNLIKELY(r0 == nb)) class_flip(r0);  // only possible for L == 0
+                if (CQ_UNLIKELY(r0 == nb)) { class_flip(r0); set_ev(r0 + 1); }  // only possible for L == 0
                 upd += 31;
                 c.out_run(ecls, C2, 32);
                 continue;
