@@ -373,6 +373,12 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     if (pb > kHullMaxPieceBlocks) pb = kHullMaxPieceBlocks;
     if (pb > p.nblk) pb = p.nblk;
     p.pb = (int)pb; p.nruns_b = (p.nblk + p.pb - 1) / p.pb;
+    // Few build CTAs (a band of a pipelined or sharded image): what matters is the chain of pushes down one run, so
+    // four warps share each run and the CTA repairs its own inner junctions. Many CTAs: one warp per run is cheaper.
+    long long nsub = strips * p.nruns_b <= (long long)di.sms * 16 ? 4 : 1;
+    if (const char* e = getenv("CHAQSDF_HULL_SUB")) nsub = atoll(e);
+    nsub = nsub >= 4 && p.pb >= 4 ? 4 : 1;
+    p.sb = (p.pb + (int)nsub - 1) / (int)nsub; p.nsub = (int)nsub;
     const int bfirst = p.out_begin >> 5, nbo = ((p.out_end - 1) >> 5) - bfirst + 1;
     long long eb = (strips * nbo + target - 1) / target;
     eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
@@ -382,10 +388,11 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     p.eb = (int)eb; p.nruns_e = (nbo + p.eb - 1) / p.eb;
     const long long gb = strips * p.nruns_b, ge = (long long)n_img * p.nstrips_e * p.nruns_e;
     if (gb > 0x7fffffffLL || ge > 0x7fffffffLL) return fail(CHAQSDF_ERR_ARG, "too many runs for one grid");
-    const size_t smem_b = hull_build_smem(p.pb), smem_e = hull_emit_smem();
+    const size_t smem_b = hull_build_smem(p.pb, p.nsub), smem_e = hull_emit_smem();
     prof_mark(0, st);
-    hull_build_kernel<<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
-    CQ_LAUNCHED("hull_build_kernel", gb, smem_b);
+    if (p.nsub == 4) hull_build4_kernel<<<(unsigned)gb, kHullWarps * 32 * 4, smem_b, st>>>(p);
+    else hull_build_kernel<<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
+    CQ_LAUNCHED(p.nsub == 4 ? "hull_build4_kernel" : "hull_build_kernel", gb, smem_b);
     prof_mark(1, st);
     if (p.nruns_b > 1 && !getenv("CHAQSDF_HULL_SEQ")) {
         const int njun = p.nruns_b - 1;

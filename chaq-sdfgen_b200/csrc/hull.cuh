@@ -9,6 +9,8 @@
 //                      run's hull words live in shared memory until the run is done, then go out as 128-byte
 //                      lines. No context rows: a run only pushes its own rows. Also leaves one flag per
 //                      (block, 32-column group): 0/1 = no site and all class 0/1, 2 = anything else.
+//   hull_build4_kernel the same for small grids: 16 warps = 4 groups x 4 sub-runs, inner junctions repaired in
+//                      shared memory by the CTA itself (shorter dependent chain per warp).
 //   hull_merge_kernel  thread = column; repairs the junctions between runs top to bottom.
 //   hull_emit_kernel   CTA = 4 warps = one strip x one run of output rows; walks the finished hull with a
 //                      cursor (hull words and g8 through L1/L2), tracks the in-column class run, quantises,
@@ -42,6 +44,7 @@ struct HullParams {
     int nstrips_e;           // strips of kEmitWarps column groups (emit kernel)
     int out_begin, out_end;
     int pb;                  // blocks per build run
+    int nsub, sb;            // a build CTA splits its run into nsub sub-runs of sb blocks (one warp each per group)
     int nruns_b;             // build runs per strip
     int eb;                  // blocks per emit run
     int nruns_e;             // emit runs per strip
@@ -49,7 +52,9 @@ struct HullParams {
     int merge_phase, merge_nphase;  // parallel merge: this launch repairs junctions k = 1 + phase + i*nphase
 };
 
-__host__ __device__ inline size_t hull_build_smem(int pb) { return (size_t)kHullWarps * (2 * 1024 + (size_t)pb * 128); }
+__host__ __device__ inline size_t hull_build_smem(int pb, int nsub) {
+    return (size_t)kHullWarps * ((size_t)nsub * 2 * 1024 + (size_t)pb * 128);
+}
 __host__ __device__ inline size_t hull_emit_smem() { return kSweepTableBytes + (size_t)kEmitWarps * kClsRing * 128; }
 
 struct HullBuildCtx {
@@ -113,35 +118,73 @@ struct HullBuildCtx {
     }
 };
 
-__global__ void __launch_bounds__(kHullWarps * 32) hull_build_kernel(HullParams p) {
+// junction repair inside a build CTA: the run's hull words are still in shared memory
+struct HullRunMergeCtx {
+    uint32_t* bits;          // run's hull words of this column (stride 32 words per block), block blk0 first
+    const uint8_t* rec_x;
+    unsigned rs32;
+    int blk0;
+    __device__ __forceinline__ uint32_t h_ld(int b) const { return bits[(b - blk0) * 32]; }
+    __device__ __forceinline__ void h_st(int b, uint32_t v) { bits[(b - blk0) * 32] = v; }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_x + (unsigned)r * rs32); }
+};
+
+// CTA = kHullWarps column groups x nsub sub-runs. Each warp builds the hull of its sub-run alone; then one warp per
+// group repairs the nsub-1 junctions inside the run, looking only at the run's own rows (triples that reach across
+// a run boundary are the merge kernel's), and the words go out. Splitting the run shortens the chain of dependent
+// pushes per warp, which is what a small band's pass 2 waits for.
+template <int NSUB>
+__device__ __forceinline__ void hull_build_body(const HullParams p) {
     extern __shared__ __align__(16) uint8_t s_hull[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cgi = warp & (kHullWarps - 1), sub = NSUB > 1 ? warp / kHullWarps : 0;
     long long id = blockIdx.x;
     const int run = (int)(id % p.nruns_b); id /= p.nruns_b;
     const int strip = (int)(id % p.nstrips);
     const int img = (int)(id / p.nstrips);
-    const int cg = strip * kHullWarps + warp;
-    if (cg >= p.ncg) return;  // whole warp; no block-level barrier below
-    uint8_t* base = s_hull + (size_t)warp * (2 * 1024 + (size_t)p.pb * 128);
-    HullBuildCtx c;
-    c.gst = base; c.gst_s = smem_u32(base);
-    c.bits = reinterpret_cast<uint32_t*>(base + 2048) + lane;
-    const uint8_t* recbase = p.inter + (long long)img * p.buf_rows * p.rs;
-    c.rec0 = recbase + cg * 32; c.rec_lane = c.rec0 + lane; c.cls0 = recbase + p.wp + cg * 4;
-    c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
-    c.rs = p.rs; c.rs32 = (unsigned)p.rs;
-    const int ncol = p.w - cg * 32;
-    c.vm = ncol >= 32 ? 0xFFFFFFFFu : ((1u << ncol) - 1u);
-    c.nrows = p.buf_rows; c.lane = lane; c.ncg = p.ncg; c.cur_blk = 0; c.slot = 0;
+    const int cg = strip * kHullWarps + cgi;
     const int b0 = run * p.pb, b1 = b0 + p.pb < p.nblk ? b0 + p.pb : p.nblk;
-    c.blk_first = b0; c.blk_end = b1;
+    const int s0 = b0 + sub * p.sb, s1 = s0 + p.sb < b1 ? s0 + p.sb : b1;
+    const bool active = cg < p.ncg;
+    if (NSUB == 1 && !active) return;  // no barrier below in this shape
+    uint32_t* gbits = reinterpret_cast<uint32_t*>(s_hull + (size_t)cgi * p.pb * 128) + lane;
+    const uint8_t* recbase = p.inter + (long long)img * p.buf_rows * p.rs;
     int lag = p.L;
     asm volatile("" : "+r"(lag));
-    HullBuild<HullBuildCtx> hb(c, lag);
-    hb.run(b0, b1, p.buf_rows);
-    uint32_t* hw = p.hull + ((long long)img * p.nblk + b0) * p.wc + cg * 32 + lane;
-    for (int i = 0; i < b1 - b0; ++i) hw[(long long)i * p.wc] = c.bits[i * 32];
+    if (active && s0 < s1) {
+        uint8_t* stage = s_hull + (size_t)kHullWarps * p.pb * 128 + (size_t)warp * 2048;
+        HullBuildCtx c;
+        c.gst = stage; c.gst_s = smem_u32(stage);
+        c.bits = gbits + (s0 - b0) * 32;
+        c.rec0 = recbase + cg * 32; c.rec_lane = c.rec0 + lane; c.cls0 = recbase + p.wp + cg * 4;
+        c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
+        c.rs = p.rs; c.rs32 = (unsigned)p.rs;
+        const int ncol = p.w - cg * 32;
+        c.vm = ncol >= 32 ? 0xFFFFFFFFu : ((1u << ncol) - 1u);
+        c.nrows = p.buf_rows; c.lane = lane; c.ncg = p.ncg; c.cur_blk = 0; c.slot = 0;
+        c.blk_first = s0; c.blk_end = s1;
+        HullBuild<HullBuildCtx> hb(c, lag);
+        hb.run(s0, s1, p.buf_rows);
+    }
+    if (NSUB > 1) {
+        __syncthreads();
+        if (active && sub == 0 && cg * 32 + lane < p.w) {
+            HullRunMergeCtx m;
+            m.bits = gbits; m.rec_x = recbase + cg * 32 + lane; m.rs32 = (unsigned)p.rs; m.blk0 = b0;
+            const int hi = (b1 * 32 < p.buf_rows ? b1 * 32 : p.buf_rows) - 1;
+            HullMerge<HullRunMergeCtx> hm(m, lag, b0 * 32, hi);
+            for (int j = b0 + p.sb; j < b1; j += p.sb) hm.junction(j * 32);
+        }
+        __syncthreads();
+    }
+    if (active) {
+        uint32_t* hw = p.hull + ((long long)img * p.nblk + s0) * p.wc + cg * 32 + lane;
+        for (int i = 0; i < s1 - s0; ++i) hw[(long long)i * p.wc] = gbits[(s0 - b0 + i) * 32];
+    }
 }
+
+__global__ void __launch_bounds__(kHullWarps * 32, 10) hull_build_kernel(HullParams p) { hull_build_body<1>(p); }
+__global__ void __launch_bounds__(kHullWarps * 32 * 4, 2) hull_build4_kernel(HullParams p) { hull_build_body<4>(p); }
 
 struct HullMergeCtx {
     uint32_t* hcol;          // hull word of block 0 of this column (stride wc per block)

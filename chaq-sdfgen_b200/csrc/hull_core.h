@@ -118,8 +118,10 @@ struct HullBuild {
 template <class Ctx>
 struct HullMerge {
     Ctx& c;
-    int L, nrows;
-    CQ_HD HullMerge(Ctx& ctx, int lag, int rows) : c(ctx), L(lag), nrows(rows) {}
+    int L;
+    int lo_row, hi_row;  // the repair looks at sites of rows [lo_row, hi_row] only (a whole buffer, or one build run)
+    CQ_HD HullMerge(Ctx& ctx, int lag, int rows) : c(ctx), L(lag), lo_row(0), hi_row(rows - 1) {}
+    CQ_HD HullMerge(Ctx& ctx, int lag, int lo, int hi) : c(ctx), L(lag), lo_row(lo), hi_row(hi) {}
     CQ_HD int height(int r) {
         const int g = (int)c.g_row(r) + 1;
         return g * g;
@@ -155,16 +157,16 @@ struct HullMerge {
     // rows < J were built (and merged) as one hull, rows >= J as another: make the union proper within 2L
     CQ_HD void junction(int J) {
         const int span = 2 * L;
-        int d1 = up(J, cq_min(nrows - 1, J + span - 1));
+        int d1 = up(J, cq_min(hi_row, J + span - 1));
         if (d1 < 0) return;
-        int u1 = down(J - 1, cq_max(0, d1 - span));
+        int u1 = down(J - 1, cq_max(lo_row, d1 - span));
         if (u1 < 0) return;
         int d1h = height(d1), u1h = height(u1);
         int u2 = -2, u2h = 0, d2 = -2, d2h = 0;  // -2: look it up
         for (;;) {
             bool changed = false;
             if (u2 == -2) {
-                u2 = down(u1 - 1, cq_max(0, d1 - span));
+                u2 = down(u1 - 1, cq_max(lo_row, d1 - span));
                 if (u2 >= 0) u2h = height(u2);
             }
             if (u2 >= 0 && cq_dominated(u2, u2h, u1, u1h, d1, d1h)) {
@@ -174,7 +176,7 @@ struct HullMerge {
                 changed = true;
             }
             if (d2 == -2) {
-                d2 = up(d1 + 1, cq_min(nrows - 1, u1 + span));
+                d2 = up(d1 + 1, cq_min(hi_row, u1 + span));
                 if (d2 >= 0) d2h = height(d2);
             }
             if (d2 >= 0 && cq_dominated(u1, u1h, d1, d1h, d2, d2h)) {

@@ -76,10 +76,12 @@ struct EmitCtx : Col {
 
 // mask: h*w bytes of 0/1. build_blocks: blocks per build run; emit_rows: rows per emit run (0 = whole column);
 // y_begin/y_end: output row range (context rows outside it still exist, as in a row-band buffer).
+// nsub > 1: every build run is built as nsub sub-runs whose junctions are repaired first, looking only at the
+// run's own rows (what one CTA of the build kernel does in shared memory), before the junctions between runs.
 // merge_order 0: junctions top to bottom; 1: in nphase = ceil(4L / run length) rounds, round i taking every
 // nphase-th junction (what the parallel merge kernel amounts to: same-round junctions cannot interact).
 extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int asym, int build_blocks, int emit_rows,
-                         int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order) {
+                         int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order, int nsub) {
     QuantTable q; build_quant_table(spread, asym, &q);
     LevelTable lt; build_level_table(q, &lt);
     const int C = lt.cap_eff, L = C - 1;
@@ -94,15 +96,28 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
     for (int x = 0; x < w; ++x) {
         std::vector<uint32_t> H(nblk, 0xdeadbeefu);
         std::vector<uint8_t> Q(nblk, 2);
+        if (nsub < 1) nsub = 1;
+        const int sb = (build_blocks + nsub - 1) / nsub;  // blocks per sub-run
         for (int b0 = 0; b0 < nblk; b0 += build_blocks) {
-            BuildCtx c;
-            c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
             const int b1 = b0 + build_blocks < nblk ? b0 + build_blocks : nblk;
-            c.b0 = b0; c.bits.assign(b1 - b0, 0xdeadbeefu);
-            HullBuild<BuildCtx> hb(c, L);
-            hb.run(b0, b1, h);
-            for (int b = b0; b < b1; ++b) H[b] = c.bits[b - b0];
-            if (c.oob) return 1000;
+            for (int s0 = b0; s0 < b1; s0 += sb) {
+                BuildCtx c;
+                c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
+                const int s1 = s0 + sb < b1 ? s0 + sb : b1;
+                c.b0 = s0; c.bits.assign(s1 - s0, 0xdeadbeefu);
+                HullBuild<BuildCtx> hb(c, L);
+                hb.run(s0, s1, h);
+                for (int b = s0; b < s1; ++b) H[b] = c.bits[b - s0];
+                if (c.oob) return 1000;
+            }
+            if (nsub > 1) {  // junctions inside the run, restricted to the run's rows
+                MergeCtx c;
+                c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
+                const int hi = (b1 * 32 < h ? b1 * 32 : h) - 1;
+                HullMerge<MergeCtx> hm(c, L, b0 * 32, hi);
+                for (int s0 = b0 + sb; s0 < b1; s0 += sb) hm.junction(s0 * 32);
+                if (c.oob) return 1500;
+            }
         }
         {
             MergeCtx c;

@@ -274,23 +274,27 @@ def emul3(tmp_path_factory):
     L = C.CDLL(so)
     u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
     L.emul3_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p,
-                            C.POINTER(C.c_int), C.c_int]
+                            C.POINTER(C.c_int), C.c_int, C.c_int]
     return L
 
 
-def _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0=0, y1=None, order=None):
-    """order None: both junction orders (top to bottom; odd then even) must give the same bytes."""
+def _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0=0, y1=None, order=None, nsub=1):
+    """order None: both junction orders (top to bottom; in rounds) and both build shapes (whole runs; four sub-runs
+    repaired inside the run first, as a CTA of the build kernel does) must give the same bytes."""
     if order is None:
         a, ce = _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0, y1, 0)
         b, _ = _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0, y1, 1)
+        c, _ = _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0, y1, 1, 4)
+        d, _ = _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0, y1, 0, 3)
         assert np.array_equal(a, b), "junction orders disagree"
+        assert np.array_equal(a, c) and np.array_equal(a, d), "sub-run builds disagree"
         return a, ce
     h, w = mask.shape
     y1 = h if y1 is None else y1
     out = np.zeros((h, w), np.uint8)
     ce = C.c_int()
     rc = L.emul3_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), build_blocks, emit_rows, y0, y1, out, C.byref(ce),
-                     order)
+                     order, nsub)
     assert rc == 0, f"emulated build/merge/emit failed (rc={rc}: 1 = cap_eff > 256, 2 = row count, >=1000 = out-of-range access)"
     return out, ce.value
 
