@@ -220,6 +220,15 @@ int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, 
     rp.above = test_above ? 1 : 0; rp.cap = spread + 1 > 256 ? 256 : (int)(spread + 1);
     rp.nwords = (int)((w + 31) / 32);
     rp.nstrips = rp.wp / 128;
+    if (rp.nwords <= 16 && !getenv("CHAQSDF_ROW8_WIDE")) {  // several rows per warp
+        int shift = 0;
+        while ((1 << shift) < rp.nwords) ++shift;
+        const size_t rows_per_cta = (size_t)kRow8Warps * (32u >> shift);
+        const unsigned blocks = (unsigned)((rows + rows_per_cta - 1) / rows_per_cta);
+        rowscan8_narrow_kernel<<<blocks, kRow8Warps * 32, 0, st>>>(rp, shift);
+        CQ_LAUNCHED("rowscan8_narrow_kernel", blocks, 0);
+        return CHAQSDF_OK;
+    }
     const size_t smem = (size_t)kRow8Warps * (rp.nwords + 1) * sizeof(uint32_t);
     const unsigned blocks = (unsigned)((rows + kRow8Warps - 1) / kRow8Warps);
     rowscan8_kernel<<<blocks, kRow8Warps * 32, smem, st>>>(rp);
@@ -377,7 +386,8 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     // four warps share each run and the CTA repairs its own inner junctions. Many CTAs: one warp per run is cheaper.
     long long nsub = strips * p.nruns_b <= (long long)di.sms * 16 ? 4 : 1;
     if (const char* e = getenv("CHAQSDF_HULL_SUB")) nsub = atoll(e);
-    nsub = nsub >= 4 && p.pb >= 4 ? 4 : 1;
+    nsub = nsub >= 4 && p.nblk >= 8 ? 4 : 1;
+    if (nsub == 4 && p.pb < 8 && !getenv("CHAQSDF_HULL_PB")) { p.pb = 8; p.nruns_b = (p.nblk + p.pb - 1) / p.pb; }  // sub-runs of >= 2 blocks
     p.sb = (p.pb + (int)nsub - 1) / (int)nsub; p.nsub = (int)nsub;
     const int bfirst = p.out_begin >> 5, nbo = ((p.out_end - 1) >> 5) - bfirst + 1;
     long long eb = (strips * nbo + target - 1) / target;

@@ -46,6 +46,40 @@ struct RowScan8Params {
     int nstrips;         // 128-column strips = wp/128; busy bytes live at record offset wp + wp/8
 };
 
+// One lane's 32-pixel word: the two ramps (distance to the nearest class change on the left / on the right), their
+// minimum clamped at cap, minus one, as 32 bytes in two 128-bit stores; then the class word.
+//   PL: last pixel left of the word with a class change immediately to its left (or -kFar)
+//   PR: first pixel right of the word with a class change immediately to its right (or >= kFar)
+__device__ __forceinline__ void row8_store(uint8_t* rec, uint32_t* crec, int wi, int x0, int nvalid, int PL, int PR,
+                                           uint32_t Lw, uint32_t R, uint32_t v, int cap) {
+    int dl[32];
+    int z = x0 - PL + 1;
+#pragma unroll
+    for (int b = 0; b < 32; ++b) {
+        z = ((Lw >> b) & 1u) ? 1 : z;
+        dl[b] = z;
+        z += 1;
+    }
+    int y = PR - (x0 + 31) + 1;
+    uint32_t packed[8];
+#pragma unroll
+    for (int b = 31; b >= 0; --b) {
+        y = ((R >> b) & 1u) ? 1 : y;
+        const int m = min(min(dl[b], y), cap) - 1;
+        if ((b & 3) == 3) packed[b >> 2] = (uint32_t)m << 24; else packed[b >> 2] |= (uint32_t)m << (8 * (b & 3));
+        y += 1;
+    }
+    if (nvalid < 32) {  // pixels past the end of the row: "none"
+#pragma unroll
+        for (int b = 0; b < 32; ++b)
+            if (b >= nvalid) packed[b >> 2] = (packed[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | ((uint32_t)(cap - 1) << (8 * (b & 3)));
+    }
+    uint4* d4 = reinterpret_cast<uint4*>(rec + x0);
+    d4[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+    d4[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    crec[wi] = v;
+}
+
 __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel(RowScan8Params p) {
     extern __shared__ uint32_t s_bits8[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -151,34 +185,71 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel
             if (lane < 8 && strip < p.nstrips) rec[p.wp + (p.wp >> 3) + strip] = ((B >> (4 * lane)) & 0xFu) ? 1 : 0;
         }
 
-        if (nvalid > 0) {
-            int dl[32];
-            int z = x0 - PL + 1;
-#pragma unroll
-            for (int b = 0; b < 32; ++b) {
-                z = ((Lw >> b) & 1u) ? 1 : z;
-                dl[b] = z;
-                z += 1;
+        if (nvalid > 0) row8_store(rec, crec, wi, x0, nvalid, PL, PR, Lw, R, v, cap);
+    }
+}
+
+// Rows of at most 512 pixels (glyph atlases: thousands of 256-pixel rows): a warp per row would leave most lanes
+// without a word, so a warp takes 32/S rows, S = lanes per row (a power of two >= nwords). Each lane loads its own
+// 32 pixels (two 128-bit loads on the fast path), so no shared memory is needed; ballots are masked to the lane's
+// row. The arithmetic per word is the wide kernel's.
+__global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_narrow_kernel(RowScan8Params p, int shift_s) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int S = 1 << shift_s, rpw = 32 >> shift_s;
+    const int seg = lane >> shift_s, wi = lane & (S - 1);
+    const long long row_w = ((long long)blockIdx.x * kRow8Warps + warp) * rpw;
+    if (row_w >= p.rows) return;  // whole warp
+    const long long row = row_w + seg;
+    const int w = p.w, x0 = wi * 32;
+    const bool above = p.above != 0;
+    const bool live = row < p.rows && wi < p.nwords;
+    int nvalid = w - x0, evalid = w - 1 - x0;
+    nvalid = !live || nvalid < 0 ? 0 : (nvalid > 32 ? 32 : nvalid);
+    evalid = !live || evalid < 0 ? 0 : (evalid > 32 ? 32 : evalid);
+
+    uint32_t v = 0u;
+    const bool fast = p.stride == 1 && (w & 15) == 0 && ((reinterpret_cast<uintptr_t>(p.img + p.offset) & 15) == 0);
+    if (nvalid > 0) {
+        const uint8_t* src = p.img + ((size_t)row * (size_t)w + (size_t)x0) * (size_t)p.stride + (size_t)p.offset;
+        if (fast) {  // nvalid is 16 or 32
+            const uint4 q = __ldg(reinterpret_cast<const uint4*>(src));
+            v = class_nibble(q.x, above) | (class_nibble(q.y, above) << 4) | (class_nibble(q.z, above) << 8) |
+                (class_nibble(q.w, above) << 12);
+            if (nvalid > 16) {
+                const uint4 r = __ldg(reinterpret_cast<const uint4*>(src) + 1);
+                v |= (class_nibble(r.x, above) | (class_nibble(r.y, above) << 4) | (class_nibble(r.z, above) << 8) |
+                      (class_nibble(r.w, above) << 12)) << 16;
             }
-            int y = PR - (x0 + 31) + 1;
-            uint32_t packed[8];
-#pragma unroll
-            for (int b = 31; b >= 0; --b) {
-                y = ((R >> b) & 1u) ? 1 : y;
-                const int m = min(min(dl[b], y), cap) - 1;
-                if ((b & 3) == 3) packed[b >> 2] = (uint32_t)m << 24; else packed[b >> 2] |= (uint32_t)m << (8 * (b & 3));
-                y += 1;
+        } else {
+            for (int b = 0; b < nvalid; ++b) {
+                const uint8_t px = __ldg(src + (size_t)b * (size_t)p.stride);
+                v |= (uint32_t)(above ? px > 127 : px < 127) << b;
             }
-            if (nvalid < 32) {  // pixels past the end of the row: "none"
-#pragma unroll
-                for (int b = 0; b < 32; ++b)
-                    if (b >= nvalid) packed[b >> 2] = (packed[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | ((uint32_t)(cap - 1) << (8 * (b & 3)));
-            }
-            uint4* d4 = reinterpret_cast<uint4*>(rec + x0);
-            d4[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-            d4[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
-            crec[wi] = v;
         }
+    }
+    const uint32_t vn = __shfl_down_sync(0xffffffffu, v, 1), vp = __shfl_up_sync(0xffffffffu, v, 1);
+    const uint32_t nbit = wi + 1 < p.nwords ? (vn & 1u) : 0u;
+    const uint32_t pbit = (wi > 0 && wi < p.nwords) ? (vp >> 31) : (v & 1u);
+    const uint32_t em = evalid == 32 ? 0xFFFFFFFFu : ((1u << evalid) - 1u);
+    const uint32_t R = (v ^ ((v >> 1) | (nbit << 31))) & em;
+    const uint32_t Lw = nvalid ? ((R << 1) | ((pbit ^ v) & 1u)) : 0u;
+    const uint32_t segmask = (S == 32 ? 0xFFFFFFFFu : ((1u << S) - 1u)) << (seg * S);
+    const uint32_t BL = __ballot_sync(0xffffffffu, Lw != 0) & segmask, BR = __ballot_sync(0xffffffffu, R != 0) & segmask;
+    const int lastL = Lw ? x0 + (31 - __clz(Lw)) : -kFar;
+    const int firstR = R ? x0 + __ffs(R) - 1 : kFar;
+    const uint32_t lt = (1u << lane) - 1u, gt = lane == 31 ? 0u : (0xFFFFFFFEu << lane);
+    const uint32_t pl = BL & lt, nr = BR & gt;
+    const int sl = __shfl_sync(0xffffffffu, lastL, pl ? 31 - __clz(pl) : 0);
+    const int sr = __shfl_sync(0xffffffffu, firstR, nr ? __ffs(nr) - 1 : 0);
+    const int PL = pl ? sl : -kFar;
+    const int PR = nr ? sr : 2 * kFar;
+    const int cap = p.cap;
+    const bool busy = nvalid > 0 && ((Lw | R) != 0u || x0 - PL + 1 < cap || PR - (x0 + nvalid - 1) + 1 < cap);
+    const uint32_t B = __ballot_sync(0xffffffffu, busy);
+    if (nvalid > 0) {
+        uint8_t* rec = p.inter + (size_t)row * (size_t)p.rs;
+        if ((wi & 3) == 0) rec[p.wp + (p.wp >> 3) + (wi >> 2)] = (B & (0xFu << lane) & segmask) ? 1 : 0;  // 4 lanes = one strip
+        row8_store(rec, reinterpret_cast<uint32_t*>(rec + p.wp), wi, x0, nvalid, PL, PR, Lw, R, v, cap);
     }
 }
 

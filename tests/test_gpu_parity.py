@@ -367,3 +367,30 @@ def test_cli_pgm_passthrough(pkg, oracle, tmp_path):
     # no alpha channel in a PGM: the default (alpha) test sees an opaque image -> all inside -> all 255
     r = subprocess.run([cli, "-i", str(src), "-o", str(dst), "-s", str(spread)], capture_output=True, timeout=120)
     assert r.returncode == 0 and (body(dst.read_bytes()) == 255).all()
+
+
+def test_narrow_rows_several_per_warp(pkg, oracle):
+    """Rows of <= 512 pixels go several to a warp in pass 1 (rowscan8_narrow_kernel): widths on both sides of every
+    lanes-per-row step, aligned (128-bit loads) and not, strided, row counts that leave a warp partly empty, batches."""
+    rng = np.random.default_rng(77)
+    for (h, w) in [(5, 16), (9, 48), (3, 64), (67, 96), (13, 128), (70, 144), (41, 256), (19, 272), (33, 496), (21, 512),
+                   (11, 500), (6, 40)]:
+        for img in (random_shapes(rng, h, w), (rng.random((h, w)) < 0.5).astype(np.uint8) * 255,
+                    rng.integers(0, 256, (h, w), dtype=np.uint8)):
+            for spread in (2, 20, 256):
+                got = gpu_u8(pkg, img, w, h, spread=spread)
+                assert np.array_equal(got, oracle.sdf(img, w, h, spread=spread)), (h, w, spread)
+    h, w = 37, 208
+    ya = rng.integers(0, 256, (h, w, 2), dtype=np.uint8)
+    ya[5:30, 20:150, :] = 220
+    for off in (0, 1):
+        for above in (True, False):
+            got = gpu_u8(pkg, ya, w, h, stride=2, offset=off, test_above=above, spread=7)
+            assert np.array_equal(got, oracle.sdf(ya, w, h, stride=2, offset=off, test_above=above, spread=7))
+    n, s = 5, 48   # 240 rows of 2 words: the last warp of the grid is partly empty
+    imgs = np.stack([random_shapes(rng, s, s) for _ in range(n)])
+    out = pkg.sdf_u8_batched_device(torch.from_numpy(imgs).cuda(), n, s, s, spread=16)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    for k in range(n):
+        assert np.array_equal(got[k], oracle.sdf(imgs[k], s, s, spread=16)), k

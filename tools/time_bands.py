@@ -1,5 +1,5 @@
 """Per-band pass-2 time on one GPU: what each rank of an N-way row-band split would spend in the envelope pass.
-usage: python tools/time_bands.py [side] [spread]"""
+usage: python tools/time_bands.py [side] [spread] [world ...]"""
 import os, sys
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -15,7 +15,8 @@ inter = torch.empty((side, rb), dtype=torch.uint8, device="cuda")
 pkg.rowscan_device(d, side, side, spread, inter)
 out = torch.empty((side, side), dtype=torch.uint8, device="cuda")
 ws = torch.empty(max(int(pkg.lib().chaqsdf_envelope_workspace_bytes(side, side, spread)), 256), dtype=torch.uint8, device="cuda")
-for world in (1, 2, 4, 8):
+worlds = [int(a) for a in sys.argv[3:]] or [1, 2, 4, 8]
+for world in worlds:
     ts = []
     for rank in range(world):
         r0, r1, ht, hb, _, _ = pkg.halo_plan(side, world, rank, spread)
