@@ -228,7 +228,8 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t[0].item())
         phases = {"rowscan_ms": float(t[1]), "halo_exchange_ms": float(t[2]), "envelope_ms": float(t[3]),
-                  "note": "per-phase CUDA-event means, max over ranks"}
+                  "halo": state.get("halo"), "note": "per-phase CUDA-event means, max over ranks; halo 'peer' = pairwise "
+                  "device-side signals + copies out of the neighbours' peer-mapped buffers over NVLink, 'p2p' = NCCL send/recv"}
     ms_step = ms_total / K
     value = h * w / (ms_step * 1e-3) / 1e6
 
@@ -258,7 +259,7 @@ def run_ours(args, rank, world, local_rank):
         e2e_s = float(t.item())
     e2e = {"value": h * w / e2e_s / 1e6, "unit": "Mpix/s", "h2d_bytes_per_step": int(h * w), "d2h_bytes_per_step": int(h * w),
            "ms_per_step": e2e_s * 1e3, "steps": Ke, "api": "chaqsdf_u8 (host buffers)" if world == 1 else
-           "H2D + sdf_u8_sharded (rowscan, NCCL halo exchange, envelope) + D2H"}
+           "H2D + sdf_u8_sharded (rowscan, halo exchange, envelope) + D2H"}
 
     if rank != 0:
         if dist is not None:

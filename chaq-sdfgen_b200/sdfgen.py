@@ -242,12 +242,56 @@ def exchange_halos(inter, h, world, rank, spread, group=None):
     return inter
 
 
+def _peer_setup(state, w, h, spread, rank, world, group, dev):
+    """Symmetric (peer-mapped) intermediates for the halo pull: every rank allocates the same [2][rows][rb] buffer
+    (two slots, alternating by call), maps its neighbours' copies over NVLink, and all ranks agree on whether that
+    worked. Returns True when the peer path is usable everywhere."""
+    import torch
+    import torch.distributed as dist
+    ok = 1
+    try:
+        import torch.distributed._symmetric_memory as symm
+        plans = [halo_plan(h, world, r, spread) for r in range(world)]
+        max_rows = max(p[2] + (p[1] - p[0]) + p[3] for p in plans)
+        rb = inter_row_bytes(w, spread)
+        sym = symm.empty((2, max_rows, rb), dtype=torch.uint8, device=dev)
+        hdl = symm.rendezvous(sym, group if group is not None else dist.group.WORLD)
+        bufs = {peer: hdl.get_buffer(peer, (2, max_rows, rb), torch.uint8) for (peer, _, _) in plans[rank][4]}
+        state.update(sym=sym, hdl=hdl, plans=plans, peer_bufs=bufs, step=0)
+    except Exception as e:  # no symmetric memory on this box / build: every rank falls back together
+        ok = 0
+        state["peer_error"] = repr(e)
+    flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return bool(flag.item())
+
+
+def pull_halos(state, slot, h, world, rank, spread, timeout_ms=20000):
+    """Peer-memory halo exchange: tell the neighbours this rank's rows of slot `slot` are written, wait for theirs,
+    then copy the halo rows straight out of their buffers over NVLink. Stream-ordered; no host synchronisation.
+    The signals pair up one to one (I signal exactly the ranks that wait for me), and the two slots make the next
+    call's pass 1 safe: it overwrites a slot only after the neighbours have signalled the call in between."""
+    hdl, plans = state["hdl"], state["plans"]
+    r0, r1, halo_top, halo_bot, recvs, sends = plans[rank]
+    base = r0 - halo_top
+    inter = state["sym"][slot]
+    for peer in sorted({p for (p, _, _) in sends}):
+        hdl.put_signal(peer, slot, timeout_ms)
+    for peer in sorted({p for (p, _, _) in recvs}):
+        hdl.wait_signal(peer, slot, timeout_ms)
+    for (peer, a, b) in recvs:
+        pbase = plans[peer][0] - plans[peer][2]  # image row held by row 0 of the peer's buffer
+        inter[a - base:b - base].copy_(state["peer_bufs"][peer][slot][a - pbase:b - pbase], non_blocking=True)
+
+
 def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, group=None, state=None, stride=1, offset=0,
-                   test_above=True, events=None):
+                   test_above=True, events=None, halo=None):
     """One image of h rows sharded by row bands over `world` ranks (one process per GPU). d_band holds this
-    rank's rows. Pass 1 is local; pass 2 needs `spread` rows of the 16-bit intermediate from each neighbour
-    band, exchanged point to point (NCCL over NVLink); then pass 2 is local. Returns this rank's output rows.
-    `state` (a dict) caches buffers between calls."""
+    rank's rows. Pass 1 is local; pass 2 needs `spread` rows of the intermediate from each neighbour band: pulled
+    out of the neighbours' peer-mapped buffers over NVLink after a pairwise device-side signal (halo "peer", the
+    default on GPUs), or exchanged point to point through NCCL / gloo (halo "p2p"; also the fallback when symmetric
+    memory cannot be set up; env CHAQSDF_HALO overrides). Then pass 2 is local. Returns this rank's output rows.
+    `state` (a dict) caches buffers between calls; state["halo"] says which exchange is in use."""
     import torch
     r0, r1, halo_top, halo_bot, _, _ = halo_plan(h, world, rank, spread)
     rows = r1 - r0
@@ -259,11 +303,22 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
     if state.get("key") != key:
         state.clear()
         state["key"] = key
-        state["inter"] = torch.empty((buf_rows, inter_row_bytes(w, spread)), dtype=torch.uint8, device=dev)
+        mode = halo or os.environ.get("CHAQSDF_HALO") or ("peer" if dev.type == "cuda" and world > 1 else "p2p")
+        if mode == "peer" and not (world > 1 and _peer_setup(state, w, h, spread, rank, world, group, dev)):
+            mode = "p2p"
+        state["halo"] = mode
+        if mode != "peer":
+            state["inter"] = torch.empty((buf_rows, inter_row_bytes(w, spread)), dtype=torch.uint8, device=dev)
         state["out"] = torch.empty((rows, w), dtype=torch.uint8, device=dev)
         nb = int(lib().chaqsdf_envelope_workspace_bytes(w, buf_rows, spread))
         state["ws"] = _workspace(nb, dev) if nb else None
-    inter, out = state["inter"], state["out"]
+    out = state["out"]
+    if state["halo"] == "peer":
+        slot = state["step"] & 1
+        state["step"] += 1
+        inter = state["sym"][slot][:buf_rows]
+    else:
+        inter = state["inter"]
     if events:
         events[0].record()
     rowscan_device(d_band, w, rows, spread, inter[halo_top:halo_top + rows], stride=stride, offset=offset,
@@ -271,7 +326,10 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
     if events:
         events[1].record()
     if world > 1:
-        exchange_halos(inter, h, world, rank, spread, group)
+        if state["halo"] == "peer":
+            pull_halos(state, slot, h, world, rank, spread)
+        else:
+            exchange_halos(inter, h, world, rank, spread, group)
     if events:
         events[2].record()
     envelope_device(inter, w, buf_rows, halo_top, halo_top + rows, spread, asymmetric, out, workspace=state["ws"])
