@@ -266,22 +266,33 @@ def _peer_setup(state, w, h, spread, rank, world, group, dev):
     return bool(flag.item())
 
 
-def pull_halos(state, slot, h, world, rank, spread, timeout_ms=20000):
+def halo_pull_list(plans, rank):
+    """The peer-memory exchange of one rank, from the halo plans of all ranks: (signal_to, wait_for, copies) with
+    copies = [(peer, dst_lo, dst_hi, src_lo, src_hi)] in buffer rows (dst in this rank's buffer, src in the peer's).
+    Only rows a peer OWNS are ever read from it, so a pull never depends on another pull."""
+    r0, r1, halo_top, halo_bot, recvs, sends = plans[rank]
+    base = r0 - halo_top
+    copies = []
+    for (peer, a, b) in recvs:
+        pbase = plans[peer][0] - plans[peer][2]  # image row held by row 0 of the peer's buffer
+        copies.append((peer, a - base, b - base, a - pbase, b - pbase))
+    return sorted({p for (p, _, _) in sends}), sorted({p for (p, _, _) in recvs}), copies
+
+
+def pull_halos(state, slot, rank, timeout_ms=20000):
     """Peer-memory halo exchange: tell the neighbours this rank's rows of slot `slot` are written, wait for theirs,
     then copy the halo rows straight out of their buffers over NVLink. Stream-ordered; no host synchronisation.
     The signals pair up one to one (I signal exactly the ranks that wait for me), and the two slots make the next
     call's pass 1 safe: it overwrites a slot only after the neighbours have signalled the call in between."""
-    hdl, plans = state["hdl"], state["plans"]
-    r0, r1, halo_top, halo_bot, recvs, sends = plans[rank]
-    base = r0 - halo_top
+    hdl = state["hdl"]
+    signal_to, wait_for, copies = halo_pull_list(state["plans"], rank)
     inter = state["sym"][slot]
-    for peer in sorted({p for (p, _, _) in sends}):
+    for peer in signal_to:
         hdl.put_signal(peer, slot, timeout_ms)
-    for peer in sorted({p for (p, _, _) in recvs}):
+    for peer in wait_for:
         hdl.wait_signal(peer, slot, timeout_ms)
-    for (peer, a, b) in recvs:
-        pbase = plans[peer][0] - plans[peer][2]  # image row held by row 0 of the peer's buffer
-        inter[a - base:b - base].copy_(state["peer_bufs"][peer][slot][a - pbase:b - pbase], non_blocking=True)
+    for (peer, d0, d1, s0, s1) in copies:
+        inter[d0:d1].copy_(state["peer_bufs"][peer][slot][s0:s1], non_blocking=True)
 
 
 def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, group=None, state=None, stride=1, offset=0,
@@ -327,7 +338,7 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
         events[1].record()
     if world > 1:
         if state["halo"] == "peer":
-            pull_halos(state, slot, h, world, rank, spread)
+            pull_halos(state, slot, rank)
         else:
             exchange_halos(inter, h, world, rank, spread, group)
     if events:

@@ -199,6 +199,35 @@ def test_halo_exchange_gloo(tmp_path, world):
     assert r.stdout.count("ok") == world
 
 
+def test_peer_halo_pull_plan_is_paired_and_complete(pkg):
+    """The peer-memory exchange (pull_halos) on paper: every signal has exactly one waiter, only owned rows are read,
+    and after the copies every rank's buffer holds image rows [r0 - halo_top, r1 + halo_bot) in order -- including
+    spreads larger than a band (multi-hop halos) and ragged band heights."""
+    for (h, world, spread) in [(64, 2, 5), (100, 3, 40), (37, 4, 3), (200, 8, 100), (33, 5, 64), (16, 4, 1), (50, 7, 50)]:
+        plans = [pkg.halo_plan(h, world, r, spread) for r in range(world)]
+        lists = [pkg.halo_pull_list(plans, r) for r in range(world)]
+        bufs = []
+        for (r0, r1, ht, hb, _, _) in plans:
+            b = np.full(ht + (r1 - r0) + hb, -1, np.int64)
+            b[ht:ht + (r1 - r0)] = np.arange(r0, r1)  # pass 1 writes the owned rows
+            bufs.append(b)
+        for r in range(world):
+            signal_to, wait_for, copies = lists[r]
+            for p in signal_to:
+                assert r in lists[p][1], (h, world, spread, r, p)
+            for p in wait_for:
+                assert r in lists[p][0], (h, world, spread, r, p)
+            assert sorted({c[0] for c in copies}) == wait_for
+        snapshot = [b.copy() for b in bufs]  # pulls read owned rows only, so their order cannot matter
+        for r in range(world):
+            for (peer, d0, d1, s0, s1) in lists[r][2]:
+                o0, o1, oht = plans[peer][0], plans[peer][1], plans[peer][2]
+                assert oht <= s0 < s1 <= oht + (o1 - o0), "reads rows the peer does not own"
+                bufs[r][d0:d1] = snapshot[peer][s0:s1]
+        for r, (r0, r1, ht, hb, _, _) in enumerate(plans):
+            assert np.array_equal(bufs[r], np.arange(r0 - ht, r1 + hb)), (h, world, spread, r)
+
+
 # ---------------------------------------------------------------- banded fast path (sweep_core.h), host emulation
 @pytest.fixture(scope="session")
 def emul2(tmp_path_factory):
