@@ -294,6 +294,13 @@ def test_host_api_pipelined_bands(pkg, oracle, monkeypatch):
     assert np.array_equal(hout.numpy(), oracle.sdf(img, n, n, spread=spread, asymmetric=True))
     monkeypatch.delenv("CHAQSDF_PIPE_ROWS")
     assert np.array_equal(pkg.sdf_u8(img, n, n, spread=spread), want)
+    # repeated calls on alternating images: a stale or early read of the pooled device buffers would show
+    flipped = np.ascontiguousarray(img[::-1, ::-1])
+    want_f = oracle.sdf(flipped, n, n, spread=spread)
+    monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "192")
+    for rep in range(6):
+        src, ref_bytes = (img, want) if rep % 2 == 0 else (flipped, want_f)
+        assert np.array_equal(pkg.sdf_u8(src, n, n, spread=spread), ref_bytes), rep
 
 
 def test_error_paths(pkg):
