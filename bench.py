@@ -26,8 +26,8 @@ sys.path.insert(0, ROOT)
 SIDE = int(os.environ.get("CHAQ_BENCH_SIDE", 16384))
 SPREAD = int(os.environ.get("CHAQ_BENCH_SPREAD", 256))
 # dram__bytes_read.sum + dram__bytes_write.sum of one hull_emit_kernel launch from the committed ncu --set full
-# capture (profiles/r01_v6_ncu_summary.txt), bytes
-TRAFFIC_EMIT = 375921408
+# capture (profiles/r01_v7_ncu_summary.txt: 152.60 MB read + 224.13 MB written), bytes
+TRAFFIC_EMIT = 376730368
 WORKLOAD = f"config4: SYN-DISCS({SIDE}) {SIDE}x{SIDE} u8 mask, spread {SPREAD}, symmetric"
 # algorithmic bytes: pass 1 reads the 1 B/px mask and writes the intermediate; pass 2 reads the
 # intermediate and writes the 1 B/px bitmap. The intermediate is 1 B/px of row distance + 1 bit/px of class
