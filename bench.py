@@ -34,8 +34,9 @@ WORKLOAD = f"config4: SYN-DISCS({SIDE}) {SIDE}x{SIDE} u8 mask, spread {SPREAD}, 
 # (spread <= 256), i.e. 2.125 B/px per pass at 16384^2; chaqsdf_inter_row_bytes gives the exact row size.
 
 
-def syn_discs(n, seed=88172645463325252, n_discs=200):
-    """SYN-DISCS(n) of SURVEY.md 8(d): xorshift64 stream -> 200 discs (cx, cy, r = 8 + rnd % (n/16))."""
+def syn_discs(n, seed=88172645463325252, n_discs=200, rows=None):
+    """SYN-DISCS(n) of SURVEY.md 8(d): xorshift64 stream -> 200 discs (cx, cy, r = 8 + rnd % (n/16)).
+    rows=(a, b): only rows [a, b) of the image (a rank's band of a large image)."""
     M = (1 << 64) - 1
     s = seed
 
@@ -46,11 +47,14 @@ def syn_discs(n, seed=88172645463325252, n_discs=200):
         s ^= (s << 17) & M
         return s
 
-    img = np.zeros((n, n), np.uint8)
+    ya, yb = rows if rows is not None else (0, n)
+    img = np.zeros((yb - ya, n), np.uint8)
     for _ in range(n_discs):
         cx, cy = rnd() % n, rnd() % n
         r = 8 + rnd() % max(n // 16, 1)
-        ys = np.arange(max(0, cy - r), min(n - 1, cy + r) + 1)
+        ys = np.arange(max(ya, cy - r), min(yb - 1, cy + r) + 1)
+        if ys.size == 0:
+            continue
         rem = r * r - (ys - cy) ** 2
         hw = np.floor(np.sqrt(rem.astype(np.float64))).astype(np.int64)
         hw += ((hw + 1) ** 2 <= rem)
@@ -58,7 +62,7 @@ def syn_discs(n, seed=88172645463325252, n_discs=200):
         x0 = np.maximum(0, cx - hw)
         x1 = np.minimum(n - 1, cx + hw)
         for y, a, b in zip(ys.tolist(), x0.tolist(), x1.tolist()):
-            img[y, a:b + 1] = 255
+            img[y - ya, a:b + 1] = 255
     return img
 
 
