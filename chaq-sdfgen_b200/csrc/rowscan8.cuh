@@ -50,8 +50,30 @@ struct RowScan8Params {
 // minimum clamped at cap, minus one, as 32 bytes in two 128-bit stores; then the class word.
 //   PL: last pixel left of the word with a class change immediately to its left (or -kFar)
 //   PR: first pixel right of the word with a class change immediately to its right (or >= kFar)
+//   flat: no word of the warp has a class change inside it (warp-uniform on purpose: a per-lane choice would make
+//         a mixed warp run both paths). Both ramps are then straight lines, and two pixels go per DPX instruction
+//         (VIADDMNMX.S16x2: min(a + b, c) on 16-bit halves), about six times fewer instructions than the bit-by-bit ramps.
 __device__ __forceinline__ void row8_store(uint8_t* rec, uint32_t* crec, int wi, int x0, int nvalid, int PL, int PR,
-                                           uint32_t Lw, uint32_t R, uint32_t v, int cap) {
+                                           uint32_t Lw, uint32_t R, uint32_t v, int cap, bool flat) {
+    uint32_t packed[8];
+    if (flat) {
+        // stored byte of pixel b = min(z0 + b, y31 + 31 - b, cap) - 1; both starts are clamped at cap first, so that
+        // every halfword stays small (<= cap + 31)
+        const uint32_t zs = (uint32_t)(min(x0 - PL + 1, cap) - 1);          // pixel 0, left ramp, minus one
+        const uint32_t ys = (uint32_t)(min(PR - (x0 + 31) + 1, cap) - 1);   // pixel 31, right ramp, minus one
+        const uint32_t z2 = zs | ((zs + 1u) << 16);                         // pixels (0, 1)
+        const uint32_t y2 = (ys + 31u) | ((ys + 30u) << 16);
+        const uint32_t c2 = (uint32_t)(cap - 1) * 0x00010001u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {  // four pixels per step: halfword pairs (4i, 4i+1) and (4i+2, 4i+3)
+            const uint32_t p0 = 4u * i, p1 = 4u * i + 2u;
+            const uint32_t up0 = p0 * 0x00010001u, up1 = p1 * 0x00010001u;                       // +p in both halves
+            const uint32_t dn0 = ((0u - p0) & 0xFFFFu) * 0x00010001u, dn1 = ((0u - p1) & 0xFFFFu) * 0x00010001u;  // -p
+            const uint32_t a = __viaddmin_s16x2(y2, dn0, __viaddmin_s16x2(z2, up0, c2));
+            const uint32_t b = __viaddmin_s16x2(y2, dn1, __viaddmin_s16x2(z2, up1, c2));
+            packed[i] = __byte_perm(a, b, 0x6420);
+        }
+    } else {
     int dl[32];
     int z = x0 - PL + 1;
 #pragma unroll
@@ -61,13 +83,13 @@ __device__ __forceinline__ void row8_store(uint8_t* rec, uint32_t* crec, int wi,
         z += 1;
     }
     int y = PR - (x0 + 31) + 1;
-    uint32_t packed[8];
 #pragma unroll
     for (int b = 31; b >= 0; --b) {
         y = ((R >> b) & 1u) ? 1 : y;
         const int m = min(min(dl[b], y), cap) - 1;
         if ((b & 3) == 3) packed[b >> 2] = (uint32_t)m << 24; else packed[b >> 2] |= (uint32_t)m << (8 * (b & 3));
         y += 1;
+    }
     }
     if (nvalid < 32) {  // pixels past the end of the row: "none"
 #pragma unroll
@@ -185,7 +207,7 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel
             if (lane < 8 && strip < p.nstrips) rec[p.wp + (p.wp >> 3) + strip] = ((B >> (4 * lane)) & 0xFu) ? 1 : 0;
         }
 
-        if (nvalid > 0) row8_store(rec, crec, wi, x0, nvalid, PL, PR, Lw, R, v, cap);
+        if (nvalid > 0) row8_store(rec, crec, wi, x0, nvalid, PL, PR, Lw, R, v, cap, (BL | BR) == 0u);
     }
 }
 
@@ -234,7 +256,8 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_narrow
     const uint32_t R = (v ^ ((v >> 1) | (nbit << 31))) & em;
     const uint32_t Lw = nvalid ? ((R << 1) | ((pbit ^ v) & 1u)) : 0u;
     const uint32_t segmask = (S == 32 ? 0xFFFFFFFFu : ((1u << S) - 1u)) << (seg * S);
-    const uint32_t BL = __ballot_sync(0xffffffffu, Lw != 0) & segmask, BR = __ballot_sync(0xffffffffu, R != 0) & segmask;
+    const uint32_t BLw = __ballot_sync(0xffffffffu, Lw != 0), BRw = __ballot_sync(0xffffffffu, R != 0);
+    const uint32_t BL = BLw & segmask, BR = BRw & segmask;
     const int lastL = Lw ? x0 + (31 - __clz(Lw)) : -kFar;
     const int firstR = R ? x0 + __ffs(R) - 1 : kFar;
     const uint32_t lt = (1u << lane) - 1u, gt = lane == 31 ? 0u : (0xFFFFFFFEu << lane);
@@ -249,7 +272,7 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_narrow
     if (nvalid > 0) {
         uint8_t* rec = p.inter + (size_t)row * (size_t)p.rs;
         if ((wi & 3) == 0) rec[p.wp + (p.wp >> 3) + (wi >> 2)] = (B & (0xFu << lane) & segmask) ? 1 : 0;  // 4 lanes = one strip
-        row8_store(rec, reinterpret_cast<uint32_t*>(rec + p.wp), wi, x0, nvalid, PL, PR, Lw, R, v, cap);
+        row8_store(rec, reinterpret_cast<uint32_t*>(rec + p.wp), wi, x0, nvalid, PL, PR, Lw, R, v, cap, (BLw | BRw) == 0u);
     }
 }
 
