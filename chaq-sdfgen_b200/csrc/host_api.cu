@@ -97,6 +97,25 @@ std::vector<size_t> pipeline_bands(size_t h, size_t cap, size_t first) {
     return v;
 }
 
+// Does chaqsdf_u8 pipeline this shape, and with which band heights (middle bands / first and last band)?
+// Bands are multiples of 32 rows, a middle band is at least 2*spread + 64 rows and the first at least spread + 32,
+// so that every band finishes some output rows (pass 2 of rows [done, b - spread) runs once row b is there).
+bool pipeline_shape(size_t w, size_t h, size_t stride, size_t spread, size_t* band_rows, size_t* first_rows) {
+    if (!(spread <= 256 && w * h >= ((size_t)1 << 22))) return false;
+    size_t band = ((size_t)32 << 20) / (w * stride);  // ~32 MB of input per band
+    if (const char* e = getenv("CHAQSDF_PIPE_ROWS")) band = (size_t)atoll(e);
+    band = (band + 31) & ~(size_t)31;
+    if (band < 2 * spread + 64) band = (2 * spread + 64 + 31) & ~(size_t)31;
+    size_t first = ((size_t)16 << 20) / (w * stride);  // ~16 MB first/last band
+    if (const char* e = getenv("CHAQSDF_PIPE_FIRST")) first = (size_t)atoll(e);
+    first = (first + 31) & ~(size_t)31;
+    if (first < spread + 32) first = (spread + 32 + 31) & ~(size_t)31;
+    if (first > band) first = band;
+    if (!(band > 0 && band * 2 <= h)) return false;
+    *band_rows = band; *first_rows = first;
+    return true;
+}
+
 int u8_pipelined(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above, size_t spread,
                  int asymmetric, uint8_t* out, size_t band_rows, size_t first_rows) {
     const size_t rs = chaqsdf_inter_row_bytes(w, spread);
@@ -166,6 +185,14 @@ __global__ void heights_to_mask_kernel(const float* __restrict__ f, uint8_t* __r
 
 extern "C" {
 
+size_t chaqsdf_pipeline_plan(size_t w, size_t h, size_t stride, size_t spread, size_t* bands, size_t max_bands) {
+    size_t band = 0, first = 0;
+    if (w == 0 || h == 0 || stride == 0 || !pipeline_shape(w, h, stride, spread, &band, &first)) return 0;
+    const std::vector<size_t> v = pipeline_bands(h, band, first);
+    for (size_t i = 0; i < v.size() && i < max_bands; ++i) bands[i] = v[i];
+    return v.size();
+}
+
 int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above, size_t spread,
                int asymmetric, uint8_t* out) {
     if (!img || !out) return set_error(CHAQSDF_ERR_ARG, "null pointer");
@@ -177,20 +204,9 @@ int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t off
     if (ws_bytes == 0) return CHAQSDF_ERR_CUDA;  // error string already set by the planner
     std::lock_guard<std::mutex> lk(g_pool.mu);
     // large images on the banded path: overlap upload, kernels and download band by band
-    if (spread <= 256 && w * h >= ((size_t)1 << 22)) {
-        size_t band = ((size_t)32 << 20) / (w * stride);  // ~32 MB of input per band
-        if (const char* e = getenv("CHAQSDF_PIPE_ROWS")) band = (size_t)atoll(e);
-        band = (band + 31) & ~(size_t)31;
-        if (band < 2 * spread + 64) band = (2 * spread + 64 + 31) & ~(size_t)31;
-        size_t first = ((size_t)16 << 20) / (w * stride);  // ~16 MB first/last band
-        if (const char* e = getenv("CHAQSDF_PIPE_FIRST")) first = (size_t)atoll(e);
-        first = (first + 31) & ~(size_t)31;
-        if (first < spread + 32) first = (spread + 32 + 31) & ~(size_t)31;
-        if (first > band) first = band;
-        if (band > 0 && band * 2 <= h) {
-            return u8_pipelined(img, w, h, stride, offset, test_above, spread, asymmetric, out, band, first);
-        }
-    }
+    size_t band = 0, first = 0;
+    if (pipeline_shape(w, h, stride, spread, &band, &first))
+        return u8_pipelined(img, w, h, stride, offset, test_above, spread, asymmetric, out, band, first);
     void *d_img, *d_out, *d_ws;
     const size_t in_bytes = w * h * stride, out_bytes = w * h;
     if (pool_get(0, in_bytes, &d_img) != cudaSuccess || pool_get(1, out_bytes, &d_out) != cudaSuccess ||

@@ -27,7 +27,7 @@ def build_library(force=False):
 
 SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "chaqsdf_profile_enable",
            "chaqsdf_profile_mean_ms", "dist_transform_2d",
-           "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
+           "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_pipeline_plan", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
            "chaqsdf_inter_row_bytes",
            "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
@@ -51,6 +51,8 @@ def lib():
     L.dist_transform_2d.argtypes = [vp, sz, sz]
     L.dist_transform_2d.restype = None
     L.chaqsdf_u8.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp]
+    L.chaqsdf_pipeline_plan.argtypes = [sz, sz, sz, sz, C.POINTER(sz), sz]
+    L.chaqsdf_pipeline_plan.restype = sz
     L.chaqsdf_workspace_bytes.argtypes = [sz, sz, sz]
     L.chaqsdf_workspace_bytes.restype = sz
     L.chaqsdf_batched_workspace_bytes.argtypes = [sz, sz, sz, sz]
@@ -128,6 +130,13 @@ def sdf_u8(img, w, h, stride=1, offset=0, test_above=True, spread=64, asymmetric
 
 
 # ---------------------------------------------------------------- device entry points (torch tensors)
+def pipeline_plan(w, h, stride=1, spread=64):
+    """Band heights (rows, top to bottom) chaqsdf_u8 uses for a host image of this shape; [] = one shot."""
+    buf = (C.c_size_t * 4096)()
+    n = int(lib().chaqsdf_pipeline_plan(w, h, stride, spread, buf, 4096))
+    return [int(buf[k]) for k in range(min(n, 4096))]
+
+
 def workspace_bytes(w, h, spread, n=1):
     return int(lib().chaqsdf_batched_workspace_bytes(n, w, h, spread))
 

@@ -68,6 +68,10 @@ int chaqsdf_dt2d_last_status(void); /* status of the calling thread's last dist_
  * 0 = luminance; sdfgen.c:264). test_above: px > 127 else px < 127 (sdfgen.c:57-59). out: host u8[w*h]. */
 int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
                size_t spread, int asymmetric, uint8_t* out);
+/* Large images (>= 4 Mpx, spread <= 256) go through chaqsdf_u8 in row bands so that upload, kernels and download
+ * overlap. This reports the schedule for a shape: the number of bands (0 = one shot) and, in bands[0..max_bands),
+ * their heights in rows, top to bottom. Host-only (no device needed); honours CHAQSDF_PIPE_ROWS / _FIRST. */
+size_t chaqsdf_pipeline_plan(size_t w, size_t h, size_t stride, size_t spread, size_t* bands, size_t max_bands);
 
 /* ---- device-resident path -------------------------------------------------------------------------
  * d_img/d_out/d_workspace are device pointers on the current device; stream is a cudaStream_t (NULL =

@@ -199,6 +199,34 @@ def test_halo_exchange_gloo(tmp_path, world):
     assert r.stdout.count("ok") == world
 
 
+def test_host_pipeline_band_schedule(pkg, monkeypatch):
+    """The row-band schedule of chaqsdf_u8 (host logic, no device): bands cover the image exactly, are multiples of
+    32 rows except the last, every band is tall enough to finish some output rows (>= spread + 32), short bands
+    come first and last, and small images or spreads beyond the banded path are not pipelined."""
+    for var in ("CHAQSDF_PIPE_ROWS", "CHAQSDF_PIPE_FIRST"):
+        monkeypatch.delenv(var, raising=False)
+    assert pkg.pipeline_plan(1024, 1024, 1, 64) == []          # < 4 Mpx
+    assert pkg.pipeline_plan(16384, 16384, 1, 1024) == []      # general path (spread > 256)
+    for (w, h, stride, spread) in [(16384, 16384, 1, 256), (16384, 16384, 2, 256), (4096, 4096, 1, 64), (2048, 2048, 1, 40),
+                                   (32768, 4000, 1, 8), (3000, 5000, 4, 200), (2048, 2049, 1, 256)]:
+        bands = pkg.pipeline_plan(w, h, stride, spread)
+        if not bands:
+            continue
+        assert sum(bands) == h, (w, h, bands)
+        assert all(b % 32 == 0 for b in bands[:-1]) and all(b > 0 for b in bands), bands
+        assert all(b >= spread + 32 for b in bands[:-1]), (spread, bands)
+        assert bands[0] <= max(bands) and len(bands) >= 2
+        assert max(bands) * w * stride <= (48 << 20) or max(bands) <= 2 * spread + 96, "a band is ~32 MB of input"
+    bands = pkg.pipeline_plan(16384, 16384, 1, 256)
+    assert len(bands) >= 8 and bands[0] < bands[len(bands) // 2] and bands[-1] < bands[len(bands) // 2], bands
+    monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "160")
+    b = pkg.pipeline_plan(2048, 2048, 1, 40)
+    assert sum(b) == 2048 and max(b) <= 160, b                # 2*spread + 64 = 144 <= 160
+    monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "64")             # too short for the context: raised to 2*spread + 64
+    b = pkg.pipeline_plan(2048, 2048, 1, 40)
+    assert sum(b) == 2048 and all(x >= 40 + 32 for x in b[:-1]), b
+
+
 def test_peer_halo_pull_plan_is_paired_and_complete(pkg):
     """The peer-memory exchange (pull_halos) on paper: every signal has exactly one waiter, only owned rows are read,
     and after the copies every rank's buffer holds image rows [r0 - halo_top, r1 + halo_bot) in order -- including
