@@ -25,6 +25,7 @@
 
 namespace chaq {
 
+#ifndef CQ_HULL_WIDE
 constexpr int kHullMaxPieceBlocks = 32;  // build runs are at most 1024 rows (int32 range of the domination test)
 
 // site b is never the minimum between its neighbours a < b < c (cross-multiplied df.c:67)
@@ -32,6 +33,16 @@ CQ_HD bool cq_dominated(int ap, int ah, int bp, int bh, int cp, int ch) {
     const int u = bp - ap, w = cp - bp;
     return w * (bh - ah) - u * (ch - bh) >= u * w * (u + w);
 }
+#else
+// Wide variant (not compiled into the library yet; tests/emul builds it to check the organisation for L up to 1024,
+// i.e. spreads beyond the banded path): u*w*(u+w) passes 2^31 once spans reach ~1300 rows, so the test is 64-bit,
+// and runs may be longer.
+constexpr int kHullMaxPieceBlocks = 128;
+CQ_HD bool cq_dominated(int ap, int ah, int bp, int bh, int cp, int ch) {
+    const long long u = bp - ap, w = cp - bp;
+    return w * (bh - ah) - u * (ch - bh) >= u * w * (u + w);
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------------------
 // build. Ctx provides:
@@ -201,7 +212,11 @@ struct HullMerge {
 //   int      q_flag(int blk)               0/1: block holds no site in any column of the group and is all class
 //                                          0/1 there; 2: anything else; 3: block outside the buffer
 //   void     out(int cls, int d2c) / void out_run(int cls, int d2c, int n)
+#ifndef CQ_HULL_WIDE
 constexpr int kClsRing = 16;  // class words kept ahead of the row being finished: ceil(L/32) + 2 <= 10
+#else
+constexpr int kClsRing = 64;  // ceil(1024/32) + 2 = 34
+#endif
 
 template <class Ctx>
 struct HullEmit {

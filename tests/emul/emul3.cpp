@@ -11,7 +11,16 @@
 
 using namespace chaq;
 
-static void rowscan_naive(const uint8_t* mask, int w, int h, int C, std::vector<uint8_t>& g8) {
+// -DCQ_HULL_WIDE: the same organisation with a 16-bit row distance and the 64-bit domination test, for L up to 1024
+#ifdef CQ_HULL_WIDE
+typedef uint16_t gval_t;
+static const int kMaxCap = 1025;
+#else
+typedef uint8_t gval_t;
+static const int kMaxCap = 256;
+#endif
+
+static void rowscan_naive(const uint8_t* mask, int w, int h, int C, std::vector<gval_t>& g8) {
     g8.resize((size_t)w * h);
     for (int y = 0; y < h; ++y) {
         const uint8_t* m = mask + (size_t)y * w;
@@ -21,17 +30,17 @@ static void rowscan_naive(const uint8_t* mask, int w, int h, int C, std::vector<
                 bool hit = (x - d >= 0 && m[x - d] != m[x]) || (x + d < w && m[x + d] != m[x]);
                 if (hit) { best = d; break; }
             }
-            g8[(size_t)y * w + x] = (uint8_t)(best - 1);
+            g8[(size_t)y * w + x] = (gval_t)(best - 1);
         }
     }
 }
 
 struct Col {
-    const uint8_t* g; const uint8_t* m; size_t stride; int nrows, nblk;
+    const gval_t* g; const uint8_t* m; size_t stride; int nrows, nblk;
     std::vector<uint32_t>* H;   // hull words of this column
     std::vector<uint8_t>* Q;    // block flags of this column (the "group" is this one column)
     long oob = 0;
-    uint32_t g_row(int r) { if (r < 0 || r >= nrows) { ++oob; return 255; } return g[(size_t)r * stride]; }
+    uint32_t g_row(int r) { if (r < 0 || r >= nrows) { ++oob; return kMaxCap - 1; } return g[(size_t)r * stride]; }
 };
 
 struct BuildCtx : Col {
@@ -86,9 +95,9 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
     LevelTable lt; build_level_table(q, &lt);
     const int C = lt.cap_eff, L = C - 1;
     if (cap_eff) *cap_eff = C;
-    if (C > 256) return 1;
+    if (C > kMaxCap) return 1;
     if (build_blocks < 1 || build_blocks > kHullMaxPieceBlocks) return 3;
-    std::vector<uint8_t> g8;
+    std::vector<gval_t> g8;
     rowscan_naive(mask, w, h, C, g8);
     const int nblk = (h + 31) / 32;
     if (emit_rows <= 0) emit_rows = h;

@@ -280,7 +280,7 @@ def _emul2_u8(L, mask, spread, asym, band, gmode=None):
     out = np.empty((h, w), np.uint8)
     ce = C.c_int()
     rc = L.emul2_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), band, out, None, C.byref(ce), gmode)
-    assert rc == 0, f"emulated banded pass failed (rc={rc}: 1 = cap_eff > 256, 2 = row count, >=1000 = stale ring access)"
+    assert rc == 0, f"emulated banded pass failed (rc={rc}: 1 = cap_eff beyond the build's limit, 2 = row count, >=1000 = stale ring access)"
     return out, ce.value
 
 
@@ -323,16 +323,26 @@ def test_banded_sweep_discs_noise_and_cap(emul2, oracle):
 
 
 # ---------------------------------------------------------------- build / merge / emit (hull_core.h), host emulation
-@pytest.fixture(scope="session")
-def emul3(tmp_path_factory):
-    so = str(tmp_path_factory.mktemp("emul3") / "libemul3.so")
-    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-o", so,
+def _build_emul3(tmp_path_factory, name, *defines):
+    so = str(tmp_path_factory.mktemp(name) / f"lib{name}.so")
+    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", *defines, "-o", so,
                     os.path.join(ROOT, "tests", "emul", "emul3.cpp")], check=True)
     L = C.CDLL(so)
     u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
     L.emul3_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p,
                             C.POINTER(C.c_int), C.c_int, C.c_int]
     return L
+
+
+@pytest.fixture(scope="session")
+def emul3(tmp_path_factory):
+    return _build_emul3(tmp_path_factory, "emul3")
+
+
+@pytest.fixture(scope="session")
+def emul3_wide(tmp_path_factory):
+    """hull_core.h with -DCQ_HULL_WIDE: 16-bit row distances, 64-bit domination test, longer class ring (L <= 1024)."""
+    return _build_emul3(tmp_path_factory, "emul3w", "-DCQ_HULL_WIDE")
 
 
 def _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0=0, y1=None, order=None, nsub=1):
@@ -352,7 +362,7 @@ def _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0=0, y1=None, ord
     ce = C.c_int()
     rc = L.emul3_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), build_blocks, emit_rows, y0, y1, out, C.byref(ce),
                      order, nsub)
-    assert rc == 0, f"emulated build/merge/emit failed (rc={rc}: 1 = cap_eff > 256, 2 = row count, >=1000 = out-of-range access)"
+    assert rc == 0, f"emulated build/merge/emit failed (rc={rc}: 1 = cap_eff beyond the build's limit, 2 = row count, >=1000 = out-of-range access)"
     return out, ce.value
 
 
@@ -393,6 +403,36 @@ def test_hull_discs_noise_and_row_ranges(emul3, oracle):
     want = oracle.sdf(img, 512, 512, spread=40)
     got, _ = _emul3_u8(emul3, (img > 127).astype(np.uint8), 40, False, 4, 96, 100, 333)
     assert np.array_equal(got[100:333], want[100:333])
+
+
+def test_hull_wide_variant_matches_oracle_beyond_the_banded_spreads(emul3_wide, oracle):
+    """Groundwork for moving spreads > 256 (config 5) from the first-generation sweep onto build / merge / emit: the
+    same core compiled wide must reproduce the oracle for reaches up to 1024 rows, for run lengths from far below
+    the reach to 128 blocks, and must agree with the narrow build where both apply."""
+    rng = np.random.default_rng(9)
+    for it in range(12):
+        h, w = int(rng.integers(200, 2600)), int(rng.integers(1, 6))
+        if it % 2 == 0:
+            yy, xx = np.mgrid[0:h, 0:w]
+            mask = np.zeros((h, w), np.uint8)
+            for _ in range(4):
+                cy, cx, r = rng.integers(0, h), rng.integers(-40, w + 40), rng.integers(1, 500)
+                mask |= ((yy - cy) ** 2 + (xx - cx) ** 2 <= r * r).astype(np.uint8)
+        else:
+            mask = (rng.random((h, w)) < rng.choice([0.0005, 0.003, 0.02, 0.5])).astype(np.uint8)
+        img = (mask * 255).astype(np.uint8)
+        for spread in (300, 700, 1024):
+            asym = bool(it & 1)
+            want = oracle.sdf(img, w, h, spread=spread, asymmetric=asym)
+            for bb, er in ((4, 0), (16, 333), (64, 1000), (128, 0)):
+                got, ce = _emul3_u8(emul3_wide, mask, spread, asym, bb, er)
+                assert ce <= spread + 1
+                assert np.array_equal(got, want), (it, h, w, spread, bb, er)
+    img = oracle.syn_discs(640)
+    m = (img > 127).astype(np.uint8)
+    for spread in (100, 256, 600):
+        got, _ = _emul3_u8(emul3_wide, m, spread, False, 8, 200)
+        assert np.array_equal(got, oracle.sdf(img, 640, 640, spread=spread)), spread
 
 
 # ---------------------------------------------------------------- chaq_sdfgen command line (reference sdfgen.c:122-244)
