@@ -19,6 +19,7 @@
 #include "sweep.cuh"
 #include "sweep_plan.cuh"
 #include "hull.cuh"
+#include "paint.cuh"
 
 using namespace chaq;
 
@@ -130,7 +131,7 @@ size_t hull_words_bytes(size_t n_img, size_t w, size_t buf_rows) {
 size_t sweep_plan_bytes(size_t n_img, size_t w, size_t buf_rows) {
     const size_t nstrips = (size_t)banded_wp(w) / 128, nblk = (buf_rows + 31) / 32, ncg = (w + 31) / 32;
     const size_t plan = align_up(n_img * nstrips * nblk, 256) + align_up((size_t)(kSweepMaxCtas + 1) * sizeof(long long), 256);
-    const size_t hull = hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256);
+    const size_t hull = 2 * hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256);  // hull + class words, flags
     return plan > hull ? plan : hull;
 }
 size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w) : w * sizeof(uint16_t); }
@@ -361,7 +362,8 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     HullParams p{};
     p.inter = d_inter; p.out = d_out; p.table = tab->dl;
     p.hull = (uint32_t*)d_ws;
-    p.flags = (uint8_t*)d_ws + hull_words_bytes(n_img, w, buf_rows);
+    p.clsT = (uint32_t*)((uint8_t*)d_ws + hull_words_bytes(n_img, w, buf_rows));
+    p.flags = (uint8_t*)d_ws + 2 * hull_words_bytes(n_img, w, buf_rows);
     p.rs = (long long)banded_rs(w); p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
     p.nblk = (int)((buf_rows + 31) / 32);
     p.ncg = (int)((w + 31) / 32); p.wc = p.ncg * 32;
@@ -425,8 +427,14 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
         CQ_LAUNCHED("hull_merge_kernel", gm, 0);
     }
     prof_mark(2, st);
-    hull_emit_kernel<<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
-    CQ_LAUNCHED("hull_emit_kernel", ge, smem_e);
+    static const bool walk = getenv("CHAQSDF_EMIT") && getenv("CHAQSDF_EMIT")[0] == 'w';
+    if (walk) {
+        hull_emit_kernel<<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
+        CQ_LAUNCHED("hull_emit_kernel", ge, smem_e);
+    } else {
+        hull_paint_kernel<<<(unsigned)ge, kEmitWarps * 32, hull_paint_smem(), st>>>(p);
+        CQ_LAUNCHED("hull_paint_kernel", ge, hull_paint_smem());
+    }
     prof_mark(3, st);
     return CHAQSDF_OK;
 }

@@ -37,6 +37,7 @@ struct HullParams {
     const LevelTable* table;
     uint32_t* hull;          // [n_img][nblk][wc] hull words
     uint8_t* flags;          // [n_img][nblk][ncg] block flags
+    uint32_t* clsT;          // [n_img][nblk][wc] class bits, transposed like the hull words (bit j = row 32*blk+j)
     long long rs;            // record stride
     int wp, w, buf_rows, nblk;
     int wc;                  // ncg * 32
@@ -65,6 +66,8 @@ struct HullBuildCtx {
     const uint8_t* rec_lane; // rec0 + lane
     const uint8_t* cls0;     // class word of buffer row 0 for this column group
     uint8_t* flag0;          // flags of block 0 for this column group (stride ncg per block)
+    uint32_t* clst0;         // transposed class word of block 0 for this lane's column (stride wc per block)
+    int wc;
     long long rs;
     unsigned rs32;
     uint32_t vm;             // columns of the group that exist
@@ -89,6 +92,7 @@ struct HullBuildCtx {
         int r = blk * 32 + lane;
         r = r < nrows ? r : nrows - 1;
         craw = __ldg(reinterpret_cast<const uint32_t*>(cls0 + (long long)r * rs));
+        clst0[(long long)blk * wc] = warp_transpose32(craw, lane);  // for the paint kernel: lane = column again
         cp_async_wait1();
         __syncwarp();
         cur_blk = blk;
@@ -158,6 +162,7 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
         c.bits = gbits + (s0 - b0) * 32;
         c.rec0 = recbase + cg * 32; c.rec_lane = c.rec0 + lane; c.cls0 = recbase + p.wp + cg * 4;
         c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
+        c.clst0 = p.clsT + (long long)img * p.nblk * p.wc + cg * 32 + lane; c.wc = p.wc;
         c.rs = p.rs; c.rs32 = (unsigned)p.rs;
         const int ncol = p.w - cg * 32;
         c.vm = ncol >= 32 ? 0xFFFFFFFFu : ((1u << ncol) - 1u);

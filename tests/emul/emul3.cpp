@@ -8,6 +8,7 @@
 #include <vector>
 #include "../../chaq-sdfgen_b200/csrc/tables.h"
 #include "../../chaq-sdfgen_b200/csrc/hull_core.h"
+#include "../../chaq-sdfgen_b200/csrc/paint_core.h"
 
 using namespace chaq;
 
@@ -76,12 +77,27 @@ struct EmitCtx : Col {
         for (int j = 0; j < 32; ++j) { int r = blk * 32 + j; if (r >= nrows) r = nrows - 1; wd |= (uint32_t)(m[(size_t)r * stride] & 1) << j; }
         return wd;
     }
+    uint32_t cls_t(int blk) { return cls_fetch(blk); }
+    void prefetch_block(int) {}
+    void prefetch_g(int) {}
+    long n_live = 0, n_dead = 0;
+    bool any(bool b) { if (b) ++n_live; else ++n_dead; return b; }
     uint32_t cls_ld(int s) { return ring[s]; }
     void cls_st(int s, uint32_t v) { ring[s] = v; }
     int q_flag(int blk) { return (blk < 0 || blk >= nblk) ? 3 : (*Q)[blk]; }
     void out(int c, int v) { d2[nout] = v; ocls[nout] = (uint8_t)c; ++nout; }
     void out_run(int c, int v, int n) { for (int i = 0; i < n; ++i) out(c, v); }
+    // owner list of the block being painted (paint_core.h); slots past 32 would be a bug
+    uint32_t seg[33];
+    void seg_st(int k, uint32_t v) { if (k < 0 || k > 32) { ++oob; return; } seg[k] = v; }
+    uint32_t seg_ld(int k) { if (k < 0 || k > 32) { ++oob; return 0; } return seg[k]; }
 };
+
+// 0: HullEmit (row-by-row walk), 1: HullPaint (plan + paint per block). Same inputs, must give the same bytes.
+static int g_emitter = 0;
+static long g_live = 0, g_dead = 0;  // (column, block) pairs painted / skipped as saturated by HullPaint
+extern "C" void emul3_paint_stats(long* live, long* dead) { *live = g_live; *dead = g_dead; g_live = g_dead = 0; }
+extern "C" void emul3_set_emitter(int e) { g_emitter = e; }
 
 // mask: h*w bytes of 0/1. build_blocks: blocks per build run; emit_rows: rows per emit run (0 = whole column);
 // y_begin/y_end: output row range (context rows outside it still exist, as in a row-band buffer).
@@ -147,8 +163,14 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
             EmitCtx c;
             c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
             c.d2 = cd2.data() + y0; c.ocls = ccls.data() + y0;
-            HullEmit<EmitCtx> he(c, L, lt.c2);
-            he.run(y0, y1);
+            if (g_emitter == 1) {
+                HullPaint<EmitCtx> hp(c, L, lt.c2);
+                hp.run(y0, y1);
+                g_live += c.n_live; g_dead += c.n_dead;
+            } else {
+                HullEmit<EmitCtx> he(c, L, lt.c2);
+                he.run(y0, y1);
+            }
             if (c.nout != y1 - y0) return 2;
             if (c.oob) return 3000;
         }
