@@ -25,9 +25,16 @@ sys.path.insert(0, ROOT)
 
 SIDE = int(os.environ.get("CHAQ_BENCH_SIDE", 16384))
 SPREAD = int(os.environ.get("CHAQ_BENCH_SPREAD", 256))
-# dram__bytes_read.sum + dram__bytes_write.sum of one hull_emit_kernel launch from the committed ncu --set full
-# capture (profiles/r01_v7_ncu_summary.txt: 152.60 MB read + 224.13 MB written), bytes
-TRAFFIC_EMIT = 376730368
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the pass-2 kernels, from the committed ncu --set full
+# capture named in TRAFFIC_SOURCE (regenerated whenever a pass-2 kernel changes). Only valid at the default side and
+# spread; omitted (null) otherwise.
+TRAFFIC_SOURCE = "profiles/r02_ncu_summary.txt"
+TRAFFIC = {"hull_build_kernel": None, "hull_paint_kernel": None}
+try:
+    with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as _f:
+        TRAFFIC.update(json.load(_f))
+except Exception:
+    pass
 WORKLOAD = f"config4: SYN-DISCS({SIDE}) {SIDE}x{SIDE} u8 mask, spread {SPREAD}, symmetric"
 # algorithmic bytes: pass 1 reads the 1 B/px mask and writes the intermediate; pass 2 reads the
 # intermediate and writes the 1 B/px bitmap. The intermediate is 1 B/px of row distance + 1 bit/px of class
@@ -276,19 +283,22 @@ def run_ours(args, rank, world, local_rank):
         p1 = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
         p2 = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
         inter_bytes = h * pkg.inter_row_bytes(w, SPREAD)
-        hull_bytes = h * w // 8  # the hull bitmask: 1 bit per pixel, written by build, read by emit
+        hull_bytes = h * w // 8  # hull bitmask and transposed class bits: 1 bit per pixel each, written by build, read by paint
         # algorithmic bytes per launch
-        bytes_of = {"rowscan8_kernel": h * w + inter_bytes, "hull_build_kernel": inter_bytes + hull_bytes,
-                    "hull_merge_par_kernel": 0, "hull_emit_kernel": inter_bytes + hull_bytes + h * w}
+        bytes_of = {"rowscan8_kernel": h * w + inter_bytes, "hull_build_kernel": inter_bytes + 2 * hull_bytes,
+                    "hull_merge_par_kernel": 0, "hull_paint_kernel": inter_bytes + 2 * hull_bytes + h * w}
         ms_of = {"rowscan8_kernel": p1, **{k: v for k, v in kernel_ms.items() if k != "calls"}}
         passes = {k: {"ms": ms_of[k], "GB/s": bytes_of[k] / (ms_of[k] * 1e-3) / 1e9 if bytes_of[k] else None,
                       "frac": bytes_of[k] / (ms_of[k] * 1e-3) / 1e9 / peak if bytes_of[k] else None,
                       "algorithmic_bytes": bytes_of[k]} for k in ms_of}
-        passes["pass2_total"] = {"ms": p2, "note": "build + junction merge (2 launches) + emit, CUDA events around the C-ABI call"}
-        dom = "hull_emit_kernel"
-        roofline = {"bound": "hbm", "kernel": dom + " (pass 2: hull walk + class run + quantise, the longest kernel)",
+        passes["pass2_total"] = {"ms": p2, "note": "build + junction merge (2 launches) + paint, CUDA events around the C-ABI call"}
+        dom = max((k for k in ms_of if bytes_of[k]), key=lambda k: ms_of[k])  # the longest kernel of the step
+        default_cfg = SIDE == 16384 and SPREAD == 256
+        roofline = {"bound": "hbm", "kernel": dom + " (the longest kernel of the step)",
                     "achieved": passes[dom]["GB/s"], "peak": peak, "unit": "GB/s", "frac": passes[dom]["frac"],
-                    "traffic": TRAFFIC_EMIT, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_of[dom],
+                    "traffic": TRAFFIC.get(dom) if default_cfg else None,
+                    "traffic_source": TRAFFIC_SOURCE if default_cfg and TRAFFIC.get(dom) else None,
+                    "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_of[dom],
                     "ms_per_launch": ms_of[dom], "launches_averaged": kernel_ms["calls"]}
     # CPU baseline: the reference's own code on this box's host cores, one bounded sample (N=1 only)
     cpu = None

@@ -16,10 +16,9 @@
 #include "envelope.cuh"
 #include "rowscan.cuh"
 #include "rowscan8.cuh"
-#include "sweep.cuh"
-#include "sweep_plan.cuh"
 #include "hull.cuh"
 #include "paint.cuh"
+#include "tuning.h"
 
 using namespace chaq;
 
@@ -49,6 +48,23 @@ int fail(int code, const std::string& msg) {
     } while (0)
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+Tuning read_tuning() {
+    Tuning t;
+    auto num = [](const char* k) { const char* e = getenv(k); return e ? atoll(e) : 0LL; };
+    t.band_rows = num("CHAQSDF_BAND_ROWS");
+    t.hull_pb = num("CHAQSDF_HULL_PB");
+    t.hull_sub = num("CHAQSDF_HULL_SUB");
+    t.hull_eb = num("CHAQSDF_HULL_EB");
+    t.hull_seq = getenv("CHAQSDF_HULL_SEQ") != nullptr;
+    t.row8_wide = getenv("CHAQSDF_ROW8_WIDE") != nullptr;
+    t.pipe_rows = num("CHAQSDF_PIPE_ROWS");
+    t.pipe_first = num("CHAQSDF_PIPE_FIRST");
+    if (const char* m = getenv("CHAQSDF_DT2D")) t.dt2d_mode = m[0] == 's' ? 1 : (m[0] == 'e' ? 2 : 0);
+    if (const char* m = getenv("CHAQSDF_GLYPH")) t.glyph = m[0] == '0' || m[0] == 'n' ? 1 : 2;
+    return t;
+}
+Tuning g_tuning = read_tuning();
 
 struct DevInfo {
     int sms = 0;
@@ -122,17 +138,15 @@ size_t banded_rs(size_t w) {
     const size_t wp = (size_t)banded_wp(w);
     return wp + wp / 8 + align_up(wp / 128, 16);
 }
-// scratch of the banded pass 2: the hull bitmask + block flags of build/merge/emit (hull.cuh), or the work split
-// of the single-sweep variant (sweep_plan.cuh: block-busy bytes + cut points); sized for either
+// scratch of the banded pass 2 (hull.cuh, paint.cuh): hull bitmask + transposed class bits (one word per
+// (32-row block, column) each) + one flag byte per (block, 32-column group)
 size_t hull_words_bytes(size_t n_img, size_t w, size_t buf_rows) {
     const size_t ncg = (w + 31) / 32, nblk = (buf_rows + 31) / 32;
     return align_up(n_img * nblk * ncg * 32 * sizeof(uint32_t), 256);
 }
-size_t sweep_plan_bytes(size_t n_img, size_t w, size_t buf_rows) {
-    const size_t nstrips = (size_t)banded_wp(w) / 128, nblk = (buf_rows + 31) / 32, ncg = (w + 31) / 32;
-    const size_t plan = align_up(n_img * nstrips * nblk, 256) + align_up((size_t)(kSweepMaxCtas + 1) * sizeof(long long), 256);
-    const size_t hull = 2 * hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256);  // hull + class words, flags
-    return plan > hull ? plan : hull;
+size_t hull_ws_bytes(size_t n_img, size_t w, size_t buf_rows) {
+    const size_t nblk = (buf_rows + 31) / 32, ncg = (w + 31) / 32;
+    return 2 * hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256);
 }
 size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w) : w * sizeof(uint16_t); }
 
@@ -158,7 +172,7 @@ int plan_envelope(size_t w, size_t buf_rows, size_t out_rows, size_t n_img, int 
     if (nb < 1) nb = 1;
     long long band = ((long long)out_rows + nb - 1) / nb;
     long long min_band = 4LL * lag;
-    if (const char* e = getenv("CHAQSDF_BAND_ROWS")) band = atoll(e), min_band = 1;
+    if (g_tuning.band_rows > 0) band = g_tuning.band_rows, min_band = 1;
     if (band < min_band) band = min_band;
     if (band > (long long)out_rows) band = (long long)out_rows;
     if (band < 1) band = 1;
@@ -221,7 +235,7 @@ int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, 
     rp.above = test_above ? 1 : 0; rp.cap = spread + 1 > 256 ? 256 : (int)(spread + 1);
     rp.nwords = (int)((w + 31) / 32);
     rp.nstrips = rp.wp / 128;
-    if (rp.nwords <= 16 && !getenv("CHAQSDF_ROW8_WIDE")) {  // several rows per warp
+    if (rp.nwords <= 16 && !g_tuning.row8_wide) {  // several rows per warp
         int shift = 0;
         while ((1 << shift) < rp.nwords) ++shift;
         const size_t rows_per_cta = (size_t)kRow8Warps * (32u >> shift);
@@ -234,109 +248,6 @@ int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, 
     const unsigned blocks = (unsigned)((rows + kRow8Warps - 1) / kRow8Warps);
     rowscan8_kernel<<<blocks, kRow8Warps * 32, smem, st>>>(rp);
     CQ_LAUNCHED("rowscan8_kernel", blocks, smem);
-    return CHAQSDF_OK;
-}
-
-// CTAs of the banded pass 2 that one SM holds, per (device, ring blocks, mode); also raises the kernel's
-// opt-in shared-memory limit (sticky per kernel, so it is only ever raised).
-std::map<std::tuple<int, int, int>, int> g_sweep_ctas;
-size_t g_sweep_smem_limit[2][64] = {{0}, {0}};
-
-template <bool GMODE>
-int sweep_ctas_per_sm(int nb, int* out) {
-    int dev = 0;
-    CQ_CUDA(cudaGetDevice(&dev));
-    std::lock_guard<std::mutex> lk(g_mu);
-    const size_t smem = sweep_smem_bytes(nb, GMODE);
-    if (dev < 64 && smem > g_sweep_smem_limit[GMODE][dev]) {
-        CQ_CUDA(cudaFuncSetAttribute(sweep_kernel<GMODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        g_sweep_smem_limit[GMODE][dev] = smem;
-    }
-    auto key = std::make_tuple(dev, nb, GMODE ? 1 : 0);
-    auto it = g_sweep_ctas.find(key);
-    if (it == g_sweep_ctas.end()) {
-        int ctas = 0;
-        CQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, sweep_kernel<GMODE>, kSweepWarps * 32, smem));
-        if (const char* e = getenv("CHAQSDF_SWEEP_CTAS"))  // tuning override: fewer resident CTAs (G mode only)
-            if (GMODE && atoi(e) > 0 && atoi(e) < ctas) ctas = atoi(e);
-        it = g_sweep_ctas.emplace(key, ctas).first;
-    }
-    *out = it->second;
-    return CHAQSDF_OK;
-}
-
-int launch_sweep(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
-                 const Tables* tab, uint8_t* d_out, void* d_plan, size_t plan_bytes, cudaStream_t st) {
-    DevInfo di;
-    if (int rc = device_info(&di)) return rc;
-    SweepParams p{};
-    p.inter = d_inter; p.out = d_out; p.table = tab->dl;
-    p.rs = (long long)banded_rs(w); p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
-    p.out_begin = (int)out_begin; p.out_end = (int)out_end;
-    p.ncg = (int)((w + 31) / 32);
-    p.nstrips = (p.ncg + kSweepWarps - 1) / kSweepWarps;
-    p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2;
-    const int nb_s = sweep_ring_blocks(p.L), nb_g = sweep_ring_blocks_g(p.L);
-    const long long out_rows = (long long)(out_end - out_begin);
-    p.total_rows = (long long)n_img * p.nstrips * out_rows;
-    // keep the whole window in shared memory when that still leaves enough warps to hide latency; otherwise
-    // stage only the push side and re-read older rows through L1/L2
-    int ctas_s = 0, ctas_g = 0;
-    bool gmode = false;
-    if (sweep_smem_bytes(nb_s, false) <= (size_t)di.max_smem_optin) {
-        if (int rc = sweep_ctas_per_sm<false>(nb_s, &ctas_s)) return rc;
-    }
-    if (ctas_s * kSweepWarps < 24) {
-        if (int rc = sweep_ctas_per_sm<true>(nb_g, &ctas_g)) return rc;
-        gmode = ctas_g > ctas_s;
-    }
-    if (const char* e = getenv("CHAQSDF_SWEEP_MODE")) {
-        if (e[0] == 'G') { if (int rc = sweep_ctas_per_sm<true>(nb_g, &ctas_g)) return rc; gmode = true; }
-        else if (e[0] == 'S' && ctas_s > 0) gmode = false;
-    }
-    p.nb = gmode ? nb_g : nb_s;
-    const int ctas = gmode ? ctas_g : ctas_s;
-    if (ctas < 1) return fail(CHAQSDF_ERR_CUDA, "banded pass 2 does not fit in shared memory");
-    long long slots = (long long)di.sms * ctas;
-    if (slots > kSweepMaxCtas) slots = kSweepMaxCtas;
-    // One run per resident CTA slot. With all slots busy the time is ~ (run + cost of the 2L context rows), which
-    // only falls as runs get shorter; the floor keeps the per-piece set-up (first block's load latency) amortised.
-    long long min_run = 64;
-    if (min_run > out_rows) min_run = out_rows;
-    long long nruns = (p.total_rows + min_run - 1) / min_run;
-    if (nruns > slots) nruns = slots;
-    const unsigned grid = (unsigned)nruns;
-    p.rows_per_cta = (p.total_rows + nruns - 1) / nruns;
-    p.cuts = nullptr;
-    const char* split = getenv("CHAQSDF_SWEEP_SPLIT");  // "rows": equal rows per CTA (for comparison)
-    if (!(split && split[0] == 'r')) {
-        // equal estimated cost per CTA: cut points from pass 1's busy bytes
-        if (!d_plan || plan_bytes < sweep_plan_bytes(n_img, w, buf_rows)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
-        SweepPlanParams q{};
-        q.inter = d_inter; q.rs = p.rs; q.flag_off = p.wp + p.wp / 8;
-        q.buf_rows = (int)buf_rows; q.nstrips = p.nstrips; q.n_img = (int)n_img;
-        q.out_begin = p.out_begin; q.out_end = p.out_end;
-        q.nblk = (int)((buf_rows + 31) / 32);
-        q.b0 = p.out_begin >> 5; q.nbo = ((p.out_end - 1) >> 5) - q.b0 + 1;
-        q.reach = (p.L + 31) / 32;
-        q.pb = (uint8_t*)d_plan;
-        q.cuts = (long long*)((char*)d_plan + align_up(n_img * (size_t)p.nstrips * q.nblk, 256));
-        q.ncta = (int)grid;
-        q.c0 = 1; q.cp = 8; q.ce = 16;
-        if (const char* e = getenv("CHAQSDF_SWEEP_COST")) sscanf(e, "%d,%d,%d", &q.c0, &q.cp, &q.ce);
-        if (q.c0 < 1) q.c0 = 1;
-        const long long nflags = (long long)n_img * q.nblk * q.nstrips;
-        const unsigned gb = (unsigned)((nflags + 255) / 256);
-        sweep_busy_kernel<<<gb, 256, 0, st>>>(q);
-        CQ_LAUNCHED("sweep_busy_kernel", gb, 0);
-        sweep_cuts_kernel<<<1, kPlanThreads, 0, st>>>(q);
-        CQ_LAUNCHED("sweep_cuts_kernel", 1, 0);
-        p.cuts = q.cuts;
-    }
-    const size_t smem = sweep_smem_bytes(p.nb, gmode);
-    if (gmode) sweep_kernel<true><<<grid, kSweepWarps * 32, smem, st>>>(p);
-    else sweep_kernel<false><<<grid, kSweepWarps * 32, smem, st>>>(p);
-    CQ_LAUNCHED(gmode ? "sweep_kernel<G>" : "sweep_kernel<S>", grid, smem);
     return CHAQSDF_OK;
 }
 
@@ -358,7 +269,7 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
                 const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st) {
     DevInfo di;
     if (int rc = device_info(&di)) return rc;
-    if (!d_ws || ws_bytes < sweep_plan_bytes(n_img, w, buf_rows)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+    if (!d_ws || ws_bytes < hull_ws_bytes(n_img, w, buf_rows)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
     HullParams p{};
     p.inter = d_inter; p.out = d_out; p.table = tab->dl;
     p.hull = (uint32_t*)d_ws;
@@ -379,7 +290,7 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     // runs of >= 2L rows need only two rounds of junction repair; shorter runs cost more in rounds than they gain
     const long long pb_par = (2 * p.L + 31) / 32;
     if (pb < pb_par) pb = pb_par;
-    if (const char* e = getenv("CHAQSDF_HULL_PB")) pb = atoll(e);
+    if (g_tuning.hull_pb > 0) pb = g_tuning.hull_pb;
     if (pb < 1) pb = 1;
     if (pb > kHullMaxPieceBlocks) pb = kHullMaxPieceBlocks;
     if (pb > p.nblk) pb = p.nblk;
@@ -387,28 +298,28 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     // Few build CTAs (a band of a pipelined or sharded image): what matters is the chain of pushes down one run, so
     // four warps share each run and the CTA repairs its own inner junctions. Many CTAs: one warp per run is cheaper.
     long long nsub = strips * p.nruns_b <= (long long)di.sms * 16 ? 4 : 1;
-    if (const char* e = getenv("CHAQSDF_HULL_SUB")) nsub = atoll(e);
+    if (g_tuning.hull_sub > 0) nsub = g_tuning.hull_sub;
     nsub = nsub >= 4 && p.nblk >= 8 ? 4 : 1;
-    if (nsub == 4 && p.pb < 8 && !getenv("CHAQSDF_HULL_PB")) { p.pb = 8; p.nruns_b = (p.nblk + p.pb - 1) / p.pb; }  // sub-runs of >= 2 blocks
+    if (nsub == 4 && p.pb < 8 && g_tuning.hull_pb <= 0) { p.pb = 8; p.nruns_b = (p.nblk + p.pb - 1) / p.pb; }  // sub-runs of >= 2 blocks
     p.sb = (p.pb + (int)nsub - 1) / (int)nsub; p.nsub = (int)nsub;
     const int bfirst = p.out_begin >> 5, nbo = ((p.out_end - 1) >> 5) - bfirst + 1;
     long long eb = (strips * nbo + target - 1) / target;
     eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
-    if (const char* e = getenv("CHAQSDF_HULL_EB")) eb = atoll(e);
+    if (g_tuning.hull_eb > 0) eb = g_tuning.hull_eb;
     if (eb < 1) eb = 1;
     if (eb > nbo) eb = nbo;
     p.eb = (int)eb; p.nruns_e = (nbo + p.eb - 1) / p.eb;
     const long long gb = strips * p.nruns_b, ge = (long long)n_img * p.nstrips_e * p.nruns_e;
     if (gb > 0x7fffffffLL || ge > 0x7fffffffLL) return fail(CHAQSDF_ERR_ARG, "too many runs for one grid");
-    const size_t smem_b = hull_build_smem(p.pb, p.nsub), smem_e = hull_emit_smem();
+    const size_t smem_b = hull_build_smem(p.pb, p.nsub), smem_e = hull_paint_smem();
     prof_mark(0, st);
     if (p.nsub == 4) hull_build4_kernel<<<(unsigned)gb, kHullWarps * 32 * 4, smem_b, st>>>(p);
     else hull_build_kernel<<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
     CQ_LAUNCHED(p.nsub == 4 ? "hull_build4_kernel" : "hull_build_kernel", gb, smem_b);
     prof_mark(1, st);
-    if (p.nruns_b > 1 && !getenv("CHAQSDF_HULL_SEQ")) {
+    if (p.nruns_b > 1 && !g_tuning.hull_seq) {
         const int njun = p.nruns_b - 1;
-        int nphase = (4 * p.L + p.pb * 32 - 1) / (p.pb * 32);  // same-launch junctions are >= 4L rows apart
+        int nphase = hull_merge_phases(p.L, p.pb);
         nphase = nphase < 1 ? 1 : (nphase > njun ? njun : nphase);
         p.merge_nphase = nphase;
         for (int phase = 0; phase < nphase; ++phase) {
@@ -427,27 +338,16 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
         CQ_LAUNCHED("hull_merge_kernel", gm, 0);
     }
     prof_mark(2, st);
-    static const bool walk = getenv("CHAQSDF_EMIT") && getenv("CHAQSDF_EMIT")[0] == 'w';
-    if (walk) {
-        hull_emit_kernel<<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
-        CQ_LAUNCHED("hull_emit_kernel", ge, smem_e);
-    } else {
-        hull_paint_kernel<<<(unsigned)ge, kEmitWarps * 32, hull_paint_smem(), st>>>(p);
-        CQ_LAUNCHED("hull_paint_kernel", ge, hull_paint_smem());
-    }
+    hull_paint_kernel<<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
+    CQ_LAUNCHED("hull_paint_kernel", ge, smem_e);
     prof_mark(3, st);
     return CHAQSDF_OK;
-}
-
-// which organisation of the banded pass 2 runs: build/merge/emit (default) or the single sweep
-bool use_hull() {
-    const char* e = getenv("CHAQSDF_PASS2");
-    return !(e && e[0] == 's');
 }
 
 }  // namespace
 
 namespace chaq {
+const Tuning& tuning() { return g_tuning; }
 int set_error(int code, const char* msg) { return fail(code, msg); }
 void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 }  // namespace chaq
@@ -460,20 +360,26 @@ extern "C" {
 int chaqsdf_version(void) { return 110; }
 const char* chaqsdf_last_error_string(void) { return g_err.c_str(); }
 unsigned long long chaqsdf_launch_count(void) { return g_launches.load(); }
+void chaqsdf_reload_tuning(void) { g_tuning = read_tuning(); }
 void chaqsdf_profile_enable(int on) { g_prof_on = on != 0; if (on) g_prof_n = 0; }
+// returns the number of calls averaged; 0 (and an error string) if there is none or a CUDA call fails
 int chaqsdf_profile_mean_ms(float ms[3]) {
-    if (!ms) return fail(CHAQSDF_ERR_ARG, "null pointer");
-    if (g_prof_n == 0) return fail(CHAQSDF_ERR_ARG, "no profiled call of the banded pass 2 yet");
+    if (!ms) { fail(CHAQSDF_ERR_ARG, "null pointer"); return 0; }
     ms[0] = ms[1] = ms[2] = 0.f;
-    for (int k = 0; k < g_prof_n; ++k) {
-        CQ_CUDA(cudaEventSynchronize(g_prof_ev[k][3]));
-        for (int i = 0; i < 3; ++i) {
+    const int n = g_prof_n < kProfSets ? g_prof_n : kProfSets;
+    if (n == 0) { fail(CHAQSDF_ERR_ARG, "no profiled call of the banded pass 2 yet"); return 0; }
+    float acc[3] = {0.f, 0.f, 0.f};
+    for (int k = 0; k < n; ++k) {
+        cudaError_t e = cudaEventSynchronize(g_prof_ev[k][3]);
+        for (int i = 0; i < 3 && e == cudaSuccess; ++i) {
             float t = 0.f;
-            CQ_CUDA(cudaEventElapsedTime(&t, g_prof_ev[k][i], g_prof_ev[k][i + 1]));
-            ms[i] += t / (float)g_prof_n;
+            e = cudaEventElapsedTime(&t, g_prof_ev[k][i], g_prof_ev[k][i + 1]);
+            acc[i] += t / (float)n;
         }
+        if (e != cudaSuccess) { fail(CHAQSDF_ERR_CUDA, std::string("profile events: ") + cudaGetErrorString(e)); return 0; }
     }
-    return g_prof_n;
+    for (int i = 0; i < 3; ++i) ms[i] = acc[i];
+    return n;
 }
 
 size_t chaqsdf_inter_row_bytes(size_t w, size_t spread) {
@@ -483,7 +389,7 @@ size_t chaqsdf_inter_row_bytes(size_t w, size_t spread) {
 
 size_t chaqsdf_batched_workspace_bytes(size_t n, size_t w, size_t h, size_t spread) {
     if (check_dims(w, h, spread) || n == 0) return 0;
-    if (banded(spread)) return align_up(n * h * banded_rs(w), 256) + sweep_plan_bytes(n, w, h);
+    if (banded(spread)) return align_up(n * h * banded_rs(w), 256) + hull_ws_bytes(n, w, h);
     EnvPlan pl;
     if (plan_envelope(w, h, h, n, cap_for(spread), &pl)) return 0;
     return align_up(n * w * h * sizeof(uint16_t), 256) + pl.ring_bytes;
@@ -493,7 +399,7 @@ size_t chaqsdf_workspace_bytes(size_t w, size_t h, size_t spread) {
 }
 size_t chaqsdf_envelope_workspace_bytes(size_t w, size_t buf_rows, size_t spread) {
     if (check_dims(w, buf_rows, spread)) return 0;
-    if (banded(spread)) return sweep_plan_bytes(1, w, buf_rows);
+    if (banded(spread)) return hull_ws_bytes(1, w, buf_rows);
     EnvPlan pl;
     if (plan_envelope(w, buf_rows, buf_rows, 1, cap_for(spread), &pl)) return 0;
     return pl.ring_bytes;
@@ -528,11 +434,8 @@ int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size
     if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     if (banded(spread)) {
         if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
-        if (use_hull())
-            return launch_hull((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
-                               workspace_bytes, (cudaStream_t)stream);
-        return launch_sweep((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
-                            workspace_bytes, (cudaStream_t)stream);
+        return launch_hull((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
+                           workspace_bytes, (cudaStream_t)stream);
     }
     EnvPlan pl;
     if (int rc = plan_envelope(w, buf_rows, out_end - out_begin, 1, cap_for(spread), &pl)) return rc;
@@ -558,13 +461,10 @@ int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t 
     if (banded(spread)) {
         if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
         const size_t inter_bytes = align_up(n * h * banded_rs(w), 256);
-        if (workspace_bytes < inter_bytes + sweep_plan_bytes(n, w, h)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+        if (workspace_bytes < inter_bytes + hull_ws_bytes(n, w, h)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
         if (int rc = launch_rowscan8(d_imgs, w, n * h, stride, offset, test_above, spread, (uint8_t*)d_workspace, st)) return rc;
-        if (use_hull())
-            return launch_hull((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
-                               workspace_bytes - inter_bytes, st);
-        return launch_sweep((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
-                            workspace_bytes - inter_bytes, st);
+        return launch_hull((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
+                           workspace_bytes - inter_bytes, st);
     }
     const int cap = cap_for(spread);
     EnvPlan pl;

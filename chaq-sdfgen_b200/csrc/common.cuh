@@ -1,0 +1,30 @@
+// common.cuh -- small device helpers shared by the kernels of the banded path.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace chaq {
+
+constexpr int kTableBytes = 2176;  // 2*260 int32 thresholds (tables.h LevelTable::thr), padded to 128
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+__device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+// 32x32 bit transpose across a warp: lane l holds row l; afterwards lane c holds column c (bit l = row l)
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+    for (int k = 16; k >= 1; k >>= 1) {
+        const uint32_t mask = k == 16 ? 0x0000FFFFu : k == 8 ? 0x00FF00FFu : k == 4 ? 0x0F0F0F0Fu : k == 2 ? 0x33333333u : 0x55555555u;
+        const uint32_t y = __shfl_xor_sync(0xffffffffu, x, k);
+        x = (lane & k) ? ((x & ~mask) | ((y >> k) & mask)) : ((x & mask) | ((y & mask) << k));
+    }
+    return x;
+}
+
+}  // namespace chaq

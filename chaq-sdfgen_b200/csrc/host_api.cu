@@ -1,18 +1,21 @@
 // host_api.cu -- host-pointer entry points of include/chaqsdf.h: the df.h:6 drop-in and the fused
-// replacement of reference openmp/sdfgen.c:261-300. They stage through a grow-only per-process device pool
-// (one lock: concurrent callers, e.g. the two OpenMP section threads of sdfgen.c:277-289, serialise) and
-// run the same device entry points as everything else. No CPU compute path.
+// replacement of reference openmp/sdfgen.c:261-300. They stage through one grow-only pool per device (one lock per
+// device: concurrent callers on the same device, e.g. the two OpenMP section threads of sdfgen.c:277-289,
+// serialise; callers on different devices do not) and run the same device entry points as everything else.
+// No CPU compute path.
 #include <cuda_runtime.h>
 
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
 
 #include "../../include/chaqsdf.h"
 #include "dt_float.cuh"
+#include "tuning.h"
 
 namespace chaq {
 int set_error(int code, const char* msg);
@@ -24,7 +27,6 @@ namespace {
 
 struct Pool {
     std::mutex mu;
-    int dev = -1;
     void* buf[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t cap[4] = {0, 0, 0, 0};
     cudaStream_t stream = nullptr;
@@ -32,18 +34,21 @@ struct Pool {
     std::vector<cudaEvent_t> ev;                   // grow-only event cache
     int* flag = nullptr;
 };
-Pool g_pool;
+std::mutex g_pools_mu;
+std::map<int, Pool*> g_pools;  // one per device, never freed (process lifetime)
 
-cudaError_t pool_get(int slot, size_t bytes, void** out) {
+// the pool of the calling thread's current device
+Pool* current_pool() {
     int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (g_pool.dev != dev) {  // device changed: drop everything (buffers belong to the old device)
-        for (int i = 0; i < 4; ++i) { g_pool.buf[i] = nullptr; g_pool.cap[i] = 0; }
-        g_pool.stream = nullptr; g_pool.flag = nullptr;
-        g_pool.s_in = g_pool.s_out = nullptr; g_pool.ev.clear();
-        g_pool.dev = dev;
-    }
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    std::lock_guard<std::mutex> lk(g_pools_mu);
+    Pool*& p = g_pools[dev];
+    if (!p) p = new Pool();
+    return p;
+}
+
+cudaError_t pool_get(Pool& g_pool, int slot, size_t bytes, void** out) {
+    cudaError_t e;
     if (!g_pool.stream) {
         e = cudaStreamCreateWithFlags(&g_pool.stream, cudaStreamNonBlocking);
         if (e != cudaSuccess) return e;
@@ -61,7 +66,15 @@ cudaError_t pool_get(int slot, size_t bytes, void** out) {
     return cudaSuccess;
 }
 
-cudaError_t pool_events(size_t n) {
+// after a failure inside the pipeline: nothing of this call may still be running when the caller gets its buffers back
+int drained(Pool& g_pool, int code, const char* msg) {
+    if (g_pool.s_in) cudaStreamSynchronize(g_pool.s_in);
+    if (g_pool.stream) cudaStreamSynchronize(g_pool.stream);
+    if (g_pool.s_out) cudaStreamSynchronize(g_pool.s_out);
+    return msg ? set_error(code, msg) : code;
+}
+
+cudaError_t pool_events(Pool& g_pool, size_t n) {
     while (g_pool.ev.size() < n) {
         cudaEvent_t e;
         cudaError_t r = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
@@ -103,11 +116,11 @@ std::vector<size_t> pipeline_bands(size_t h, size_t cap, size_t first) {
 bool pipeline_shape(size_t w, size_t h, size_t stride, size_t spread, size_t* band_rows, size_t* first_rows) {
     if (!(spread <= 256 && w * h >= ((size_t)1 << 22))) return false;
     size_t band = ((size_t)32 << 20) / (w * stride);  // ~32 MB of input per band
-    if (const char* e = getenv("CHAQSDF_PIPE_ROWS")) band = (size_t)atoll(e);
+    if (chaq::tuning().pipe_rows > 0) band = (size_t)chaq::tuning().pipe_rows;
     band = (band + 31) & ~(size_t)31;
     if (band < 2 * spread + 64) band = (2 * spread + 64 + 31) & ~(size_t)31;
     size_t first = ((size_t)16 << 20) / (w * stride);  // ~16 MB first/last band
-    if (const char* e = getenv("CHAQSDF_PIPE_FIRST")) first = (size_t)atoll(e);
+    if (chaq::tuning().pipe_first > 0) first = (size_t)chaq::tuning().pipe_first;
     first = (first + 31) & ~(size_t)31;
     if (first < spread + 32) first = (spread + 32 + 31) & ~(size_t)31;
     if (first > band) first = band;
@@ -116,13 +129,13 @@ bool pipeline_shape(size_t w, size_t h, size_t stride, size_t spread, size_t* ba
     return true;
 }
 
-int u8_pipelined(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above, size_t spread,
+int u8_pipelined(Pool& g_pool, const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above, size_t spread,
                  int asymmetric, uint8_t* out, size_t band_rows, size_t first_rows) {
     const size_t rs = chaqsdf_inter_row_bytes(w, spread);
     const size_t plan_bytes = chaqsdf_envelope_workspace_bytes(w, h, spread);
     void *d_img, *d_out, *d_inter, *d_plan;
-    if (pool_get(0, w * h * stride, &d_img) != cudaSuccess || pool_get(1, w * h, &d_out) != cudaSuccess ||
-        pool_get(2, rs * h, &d_inter) != cudaSuccess || pool_get(3, plan_bytes ? plan_bytes : 256, &d_plan) != cudaSuccess)
+    if (pool_get(g_pool, 0, w * h * stride, &d_img) != cudaSuccess || pool_get(g_pool, 1, w * h, &d_out) != cudaSuccess ||
+        pool_get(g_pool, 2, rs * h, &d_inter) != cudaSuccess || pool_get(g_pool, 3, plan_bytes ? plan_bytes : 256, &d_plan) != cudaSuccess)
         return set_error(CHAQSDF_ERR_CUDA, "device allocation failed");
     if (!g_pool.s_in) {
         if (cudaStreamCreateWithFlags(&g_pool.s_in, cudaStreamNonBlocking) != cudaSuccess ||
@@ -131,7 +144,7 @@ int u8_pipelined(const uint8_t* img, size_t w, size_t h, size_t stride, size_t o
     }
     const std::vector<size_t> bands = pipeline_bands(h, band_rows, first_rows);
     const size_t nbands = bands.size();
-    if (pool_events(2 * nbands) != cudaSuccess) return set_error(CHAQSDF_ERR_CUDA, "event creation failed");
+    if (pool_events(g_pool, 2 * nbands) != cudaSuccess) return set_error(CHAQSDF_ERR_CUDA, "event creation failed");
     cudaStream_t s_in = g_pool.s_in, s_cmp = g_pool.stream, s_out = g_pool.s_out;
     const uint8_t* dimg = (const uint8_t*)d_img;
     uint8_t* dinter = (uint8_t*)d_inter;
@@ -145,24 +158,24 @@ int u8_pipelined(const uint8_t* img, size_t w, size_t h, size_t stride, size_t o
         if (cudaMemcpyAsync((void*)(dimg + a * row_bytes), img + a * row_bytes, (b - a) * row_bytes, cudaMemcpyHostToDevice,
                             s_in) != cudaSuccess || cudaEventRecord(ev_in, s_in) != cudaSuccess ||
             cudaStreamWaitEvent(s_cmp, ev_in, 0) != cudaSuccess)
-            return set_error(CHAQSDF_ERR_CUDA, "upload failed");
+            return drained(g_pool, CHAQSDF_ERR_CUDA, "upload failed");
         int rc = chaqsdf_rowscan_device(dimg + a * row_bytes, w, b - a, stride, offset, test_above, spread, dinter + a * rs, s_cmp);
-        if (rc) return rc;
+        if (rc) return drained(g_pool, rc, nullptr);
         const size_t upto = b == h ? h : (b > spread ? b - spread : 0);
         if (upto > done) {
             size_t top = done > spread ? done - spread : 0;
             top &= ~(size_t)31;
             rc = chaqsdf_envelope_device(dinter + top * rs, w, b - top, done - top, upto - top, spread, asymmetric,
                                          dout + done * w, d_plan, plan_bytes, s_cmp);
-            if (rc) return rc;
+            if (rc) return drained(g_pool, rc, nullptr);
             if (cudaEventRecord(ev_cmp, s_cmp) != cudaSuccess || cudaStreamWaitEvent(s_out, ev_cmp, 0) != cudaSuccess ||
                 cudaMemcpyAsync(out + done * w, dout + done * w, (upto - done) * w, cudaMemcpyDeviceToHost, s_out) != cudaSuccess)
-                return set_error(CHAQSDF_ERR_CUDA, "download failed");
+                return drained(g_pool, CHAQSDF_ERR_CUDA, "download failed");
             done = upto;
         }
     }
     if (cudaStreamSynchronize(s_out) != cudaSuccess || cudaStreamSynchronize(s_cmp) != cudaSuccess)
-        return set_error(CHAQSDF_ERR_CUDA, "pipeline failed");
+        return drained(g_pool, CHAQSDF_ERR_CUDA, "pipeline failed");
     return CHAQSDF_OK;
 }
 
@@ -202,33 +215,38 @@ int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t off
     if (spread == 0) return set_error(CHAQSDF_ERR_ARG, "spread must be a positive integer");
     const size_t ws_bytes = chaqsdf_workspace_bytes(w, h, spread);
     if (ws_bytes == 0) return CHAQSDF_ERR_CUDA;  // error string already set by the planner
+    Pool* pool = current_pool();
+    if (!pool) return set_error(CHAQSDF_ERR_CUDA, "no current CUDA device");
+    Pool& g_pool = *pool;
     std::lock_guard<std::mutex> lk(g_pool.mu);
     // large images on the banded path: overlap upload, kernels and download band by band
     size_t band = 0, first = 0;
     if (pipeline_shape(w, h, stride, spread, &band, &first))
-        return u8_pipelined(img, w, h, stride, offset, test_above, spread, asymmetric, out, band, first);
+        return u8_pipelined(g_pool, img, w, h, stride, offset, test_above, spread, asymmetric, out, band, first);
     void *d_img, *d_out, *d_ws;
     const size_t in_bytes = w * h * stride, out_bytes = w * h;
-    if (pool_get(0, in_bytes, &d_img) != cudaSuccess || pool_get(1, out_bytes, &d_out) != cudaSuccess ||
-        pool_get(2, ws_bytes, &d_ws) != cudaSuccess)
+    if (pool_get(g_pool, 0, in_bytes, &d_img) != cudaSuccess || pool_get(g_pool, 1, out_bytes, &d_out) != cudaSuccess ||
+        pool_get(g_pool, 2, ws_bytes, &d_ws) != cudaSuccess)
         return set_error(CHAQSDF_ERR_CUDA, "device allocation failed");
     cudaStream_t st = g_pool.stream;
-    if (cudaMemcpyAsync(d_img, img, in_bytes, cudaMemcpyHostToDevice, st) != cudaSuccess) return CHAQSDF_ERR_CUDA;
+    if (cudaMemcpyAsync(d_img, img, in_bytes, cudaMemcpyHostToDevice, st) != cudaSuccess)
+        return drained(g_pool, CHAQSDF_ERR_CUDA, "upload failed");
     int rc = chaqsdf_u8_device((const uint8_t*)d_img, w, h, stride, offset, test_above, spread, asymmetric,
                                (uint8_t*)d_out, d_ws, ws_bytes, st);
-    if (rc) return rc;
-    if (cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, st) != cudaSuccess) return CHAQSDF_ERR_CUDA;
-    if (cudaStreamSynchronize(st) != cudaSuccess) return CHAQSDF_ERR_CUDA;
+    if (rc) return drained(g_pool, rc, nullptr);
+    if (cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        return drained(g_pool, CHAQSDF_ERR_CUDA, "download failed");
+    if (cudaStreamSynchronize(st) != cudaSuccess) return set_error(CHAQSDF_ERR_CUDA, "stream synchronisation failed");
     return CHAQSDF_OK;
 }
 
 // General heights (or CHAQSDF_DT2D=stock): the reference's float32 envelope, one thread per line (dt_float.cuh).
 // d_f holds the image on the device; on success it holds the result.
-static int dt2d_float_device(float* d_f, size_t w, size_t h, cudaStream_t st) {
+static int dt2d_float_device(Pool& g_pool, float* d_f, size_t w, size_t h, cudaStream_t st) {
     const size_t n = w * h;
     void *d_tmp, *d_v, *d_z;
-    if (pool_get(1, n * sizeof(float), &d_tmp) != cudaSuccess || pool_get(2, n * sizeof(int), &d_v) != cudaSuccess ||
-        pool_get(3, n * sizeof(float), &d_z) != cudaSuccess)
+    if (pool_get(g_pool, 1, n * sizeof(float), &d_tmp) != cudaSuccess || pool_get(g_pool, 2, n * sizeof(int), &d_v) != cudaSuccess ||
+        pool_get(g_pool, 3, n * sizeof(float), &d_z) != cudaSuccess)
         return set_error(CHAQSDF_ERR_CUDA, "device allocation failed");
     chaq::DtFloatParams p;
     p.v = (int*)d_v; p.z = (float*)d_z;
@@ -252,12 +270,15 @@ void dist_transform_2d(float* img, size_t w, size_t h) {
     if (!img || w == 0 || h == 0) return;
     const size_t ws_bytes = chaqsdf_fields_workspace_bytes(w, h);
     if (ws_bytes == 0) { g_dt_status = CHAQSDF_ERR_CUDA; return; }
+    Pool* pool = current_pool();
+    if (!pool) { g_dt_status = CHAQSDF_ERR_CUDA; return; }
+    Pool& g_pool = *pool;
     std::lock_guard<std::mutex> lk(g_pool.mu);
     void *d_f, *d_mask, *d_ws;
     const size_t n = w * h;
     g_dt_status = CHAQSDF_ERR_CUDA;
-    if (pool_get(0, n * sizeof(float), &d_f) != cudaSuccess || pool_get(1, n, &d_mask) != cudaSuccess ||
-        pool_get(2, ws_bytes, &d_ws) != cudaSuccess)
+    if (pool_get(g_pool, 0, n * sizeof(float), &d_f) != cudaSuccess || pool_get(g_pool, 1, n, &d_mask) != cudaSuccess ||
+        pool_get(g_pool, 2, ws_bytes, &d_ws) != cudaSuccess)
         return;
     cudaStream_t st = g_pool.stream;
     if (cudaMemsetAsync(g_pool.flag, 0, sizeof(int), st) != cudaSuccess) return;
@@ -269,11 +290,10 @@ void dist_transform_2d(float* img, size_t w, size_t h) {
     int flag = 0;
     if (cudaMemcpyAsync(&flag, g_pool.flag, sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess) return;
     if (cudaStreamSynchronize(st) != cudaSuccess) return;
-    const char* mode = getenv("CHAQSDF_DT2D");
-    if (flag || (mode && mode[0] == 's')) {  // sampled function, or stock-compatible float32 output asked for
+    if (flag || chaq::tuning().dt2d_mode == 1) {  // sampled function, or stock-compatible float32 output asked for
         if (w > CHAQSDF_MAX_DIM || h > CHAQSDF_MAX_DIM) { g_dt_status = set_error(CHAQSDF_ERR_ARG, "image side exceeds 32768"); return; }
         if (n == 1) { g_dt_status = CHAQSDF_OK; return; }  // df.c:32-36: a single cell is returned as it is
-        int rc = dt2d_float_device((float*)d_f, w, h, st);
+        int rc = dt2d_float_device(g_pool, (float*)d_f, w, h, st);
         if (rc) { g_dt_status = rc; return; }
         if (cudaMemcpyAsync(img, d_f, n * sizeof(float), cudaMemcpyDeviceToHost, st) != cudaSuccess) return;
         if (cudaStreamSynchronize(st) != cudaSuccess) return;

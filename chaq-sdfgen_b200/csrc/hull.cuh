@@ -1,5 +1,5 @@
-// hull.cuh -- pass 2, banded fast path (spread <= 256), organised as build / merge / emit over a hull bitmask in
-// global memory (hull_core.h). Replaces dist_transform_axis #2 (reference openmp/df.c:133 -> df.c:29-97, incl.
+// hull.cuh -- pass 2, banded fast path (spread <= 256): build and merge of the hull bitmask in global memory
+// (hull_core.h); the evaluation is paint.cuh. Replaces dist_transform_axis #2 (reference openmp/df.c:133 -> df.c:29-97, incl.
 // the sqrtf at df.c:95) for the inside and the outside field of openmp/sdfgen.c:277-289, and fuses
 // transform_float_sub (sdfgen.c:98-106) and transform_float_to_byte (sdfgen.c:75-96) as an exact integer
 // threshold look-up (tables.h).
@@ -12,15 +12,13 @@
 //   hull_build4_kernel the same for small grids: 16 warps = 4 groups x 4 sub-runs, inner junctions repaired in
 //                      shared memory by the CTA itself (shorter dependent chain per warp).
 //   hull_merge_kernel  thread = column; repairs the junctions between runs top to bottom.
-//   hull_emit_kernel   CTA = 4 warps = one strip x one run of output rows; walks the finished hull with a
-//                      cursor (hull words and g8 through L1/L2), tracks the in-column class run, quantises,
-//                      and writes whole blocks at once where the flags say nothing is within reach.
+//   hull_merge_par_kernel  thread = (junction, column); junctions of one launch are far enough apart to be independent.
 // Grids are one CTA per run (thousands), so the hardware scheduler balances dense and empty areas.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "hull_core.h"
-#include "sweep.cuh"  // cp_async16, cp_async_commit, cp_async_wait1, warp_transpose32, smem_u32, kSweepTableBytes
+#include "common.cuh"
 #include "tables.h"
 
 namespace chaq {
@@ -56,7 +54,6 @@ struct HullParams {
 __host__ __device__ inline size_t hull_build_smem(int pb, int nsub) {
     return (size_t)kHullWarps * ((size_t)nsub * 2 * 1024 + (size_t)pb * 128);
 }
-__host__ __device__ inline size_t hull_emit_smem() { return kSweepTableBytes + (size_t)kEmitWarps * kClsRing * 128; }
 
 struct HullBuildCtx {
     const uint8_t* gst;      // staging (2 blocks of 32 rows x 32 bytes), generic pointer at lane 0
@@ -232,111 +229,6 @@ __global__ void __launch_bounds__(256) hull_merge_par_kernel(HullParams p) {
     c.rs32 = (unsigned)p.rs; c.wc = p.wc;
     HullMerge<HullMergeCtx> hm(c, p.L, p.buf_rows);
     hm.junction(k * p.pb * 32);
-}
-
-struct HullEmitCtx {
-    const uint32_t* hcol;    // hull word of block 0 of this column
-    const uint8_t* rec_lane;
-    const uint8_t* cls0;
-    const uint8_t* flag0;
-    uint32_t* cring;         // class ring, already offset by lane
-    long long rs;
-    unsigned rs32;
-    int wc, ncg, nrows, nblk, lane;
-    // epilogue (see sweep.cuh)
-    const int32_t* thr;
-    uint8_t* optr;
-    bool store_ok;
-    long long ostride;
-    int qcls, qm, qlo, qhi, qbyte, qsign;
-    const int32_t* qthr;
-
-    __device__ __forceinline__ uint32_t h_ld(int b) const { return b < nblk ? __ldg(hcol + (long long)b * wc) : 0u; }
-    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_lane + (unsigned)r * rs32); }
-    __device__ __forceinline__ uint32_t cls_fetch(int blk) const {
-        int r = blk * 32 + lane;
-        r = r < nrows ? r : nrows - 1;
-        const uint32_t raw = __ldg(reinterpret_cast<const uint32_t*>(cls0 + (long long)r * rs));
-        return warp_transpose32(raw, lane);
-    }
-    __device__ __forceinline__ uint32_t cls_ld(int s) const { return cring[s * 32]; }
-    __device__ __forceinline__ void cls_st(int s, uint32_t v) { cring[s * 32] = v; }
-    __device__ __forceinline__ int q_flag(int blk) const {
-        return (blk < 0 || blk >= nblk) ? 3 : (int)__ldg(flag0 + (long long)blk * ncg);
-    }
-    __device__ __forceinline__ void requant(int cls, int d2c) {
-        if (cls != qcls) {
-            qcls = cls;
-            qthr = thr + cls * 260;
-            qsign = cls ? 1 : -1;
-            qm = level_of(qthr, d2c);
-        } else {
-            while (d2c >= qthr[qm + 1]) ++qm;
-            while (d2c < qthr[qm]) --qm;
-        }
-        qlo = qthr[qm];
-        qhi = qthr[qm + 1];
-        qbyte = cls ? qm : 255 - qm;
-    }
-    __device__ __forceinline__ void out(int cls, int d2c) {
-        const int step = (d2c >= qhi ? 1 : 0) - (d2c < qlo ? 1 : 0);
-        if (step != 0) {
-            qm += step;
-            qbyte += step * qsign;
-            qlo = qthr[qm];
-            qhi = qthr[qm + 1];
-        }
-        if (CQ_UNLIKELY(d2c >= qhi || d2c < qlo || cls != qcls)) requant(cls, d2c);
-        if (store_ok) *optr = (uint8_t)qbyte;
-        optr += ostride;
-    }
-    __device__ __forceinline__ void out_run(int cls, int d2c, int n) {
-        out(cls, d2c);
-        const uint8_t b = (uint8_t)qbyte;
-        for (int i = 1; i < n; ++i) {
-            if (store_ok) *optr = b;
-            optr += ostride;
-        }
-    }
-};
-
-#ifndef CQ_EMIT_MINB
-#define CQ_EMIT_MINB 9
-#endif
-__global__ void __launch_bounds__(kEmitWarps * 32, CQ_EMIT_MINB) hull_emit_kernel(HullParams p) {
-    extern __shared__ __align__(16) uint8_t s_hull[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int32_t* s_thr = reinterpret_cast<int32_t*>(s_hull);
-    for (int i = threadIdx.x; i < 2 * 260; i += kEmitWarps * 32) s_thr[i] = (&p.table->thr[0][0])[i];
-    __syncthreads();
-    long long id = blockIdx.x;
-    const int run = (int)(id % p.nruns_e); id /= p.nruns_e;
-    const int strip = (int)(id % p.nstrips_e);
-    const int img = (int)(id / p.nstrips_e);
-    const int cg = strip * kEmitWarps + warp;
-    if (cg >= p.ncg) return;
-    // runs are cut at multiples of 32 buffer rows so that whole blocks can be written at once
-    const int bfirst = p.out_begin >> 5;
-    int y0 = (bfirst + run * p.eb) * 32, y1 = y0 + p.eb * 32;
-    y0 = y0 > p.out_begin ? y0 : p.out_begin;
-    y1 = y1 < p.out_end ? y1 : p.out_end;
-    if (y0 >= y1) return;
-    HullEmitCtx c;
-    const int x = cg * 32 + lane;
-    c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
-    const uint8_t* recbase = p.inter + (long long)img * p.buf_rows * p.rs;
-    c.rec_lane = recbase + x; c.cls0 = recbase + p.wp + cg * 4;
-    c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
-    c.cring = reinterpret_cast<uint32_t*>(s_hull + kSweepTableBytes + (size_t)warp * kClsRing * 128) + lane;
-    c.rs = p.rs; c.rs32 = (unsigned)p.rs; c.wc = p.wc; c.ncg = p.ncg; c.nrows = p.buf_rows; c.nblk = p.nblk; c.lane = lane;
-    c.thr = s_thr; c.ostride = p.w; c.store_ok = x < p.w;
-    const int out_rows = p.out_end - p.out_begin;
-    c.optr = p.out + ((long long)img * out_rows + (y0 - p.out_begin)) * (long long)p.w + (x < p.w ? x : 0);
-    c.qcls = -1; c.qm = 1; c.qlo = 0; c.qhi = 0x7fffffff; c.qbyte = 0; c.qsign = 1; c.qthr = s_thr;
-    int lag = p.L;
-    asm volatile("" : "+r"(lag));
-    HullEmit<HullEmitCtx> he(c, lag, p.c2);
-    he.run(y0, y1);
 }
 
 }  // namespace chaq

@@ -1,12 +1,26 @@
-// hull_core.h -- the banded column pass (pass 2) as three steps over a hull bitmask in global memory, written
-// once for host and device. Same mathematics as sweep_core.h (see there for the proof that ONE lower envelope
-// over heights G^2 serves both classes); different organisation, after the band structure of PBA (Cao et al.):
+// hull_core.h -- the banded column pass (pass 2) as build / merge over a hull bitmask in global memory, written once
+// for host and device; the evaluation of the finished hull is paint_core.h. After the band structure of PBA (Cao et al.).
+//
+// Replaces the second dist_transform_axis call (reference openmp/df.c:133 -> dist_transform_1d, df.c:29-97) for BOTH
+// fields of openmp/sdfgen.c:277-289, in exact integer arithmetic.
+//
+// Input per column and row r (from pass 1): the pixel's class c(r) and G(r) = distance along the row to the nearest
+// pixel of the OTHER class, stored as g8 = min(G, C) - 1 (C = cap_eff of tables.h, g8 == C-1: none within reach).
+// A pixel of class c at row y needs D2(y) = min over opposite-class pixels q of |p - q|^2. One lower envelope serves
+// both classes:
+//     D2(y) = min( V(y)^2 , min_r (y - r)^2 + G(r)^2 )             (clamped at C^2)
+// where V(y) is the distance along the column to the nearest row of the other class and r runs over ALL rows
+// regardless of class. Proof sketch: for r of y's class the term is the squared distance to a real opposite pixel
+// (the one G(r) points at); for r of the other class the term is >= (y-r)^2 >= V(y)^2; and the true nearest opposite
+// pixel is either in y's column (V) or is the row-nearest opposite pixel of a same-class row. So the class bit
+// matters only for V and for the sign of the result, and the envelope is the plain Felzenszwalb-Huttenlocher one
+// (df.c:57-79) over heights G^2, kept as a bitmask of "rows on the hull".
 //
 //   build   each (32-column group, run of <= 1024 rows) builds the Felzenszwalb-Huttenlocher hull of ITS rows only
 //           (reference openmp/df.c:57-79, integer cross-multiplied domination test), no context rows;
-//   merge   per column, the junctions between consecutive runs are repaired top to bottom: sites next to a
-//           junction that are dominated across it are removed (alternating pops on both sides);
-//   emit    each (group, run of rows) walks the finished, immutable hull (df.c:83-96) with a cursor, adds the
+//   merge   per column, the junctions between consecutive runs are repaired: sites next to a junction that are
+//           dominated across it are removed (alternating pops on both sides);
+//   paint   (paint_core.h) each (group, run of rows) evaluates the finished, immutable hull (df.c:83-96), adds the
 //           in-column distance V to the nearest row of the other class, clamps at C^2 and quantises.
 //
 // Because every height is < C^2 and every result is clamped at C^2 = (L+1)^2, only triples of consecutive
@@ -18,12 +32,16 @@
 //
 // The hull is one bit per pixel, word (32-row block b, column x); g8 is re-read from pass 1's record whenever
 // a site's height is needed again. All int32: spans <= 1024 rows, heights <= 2^16 -> |terms| < 2^29.
+// The same source is compiled by g++ in tests/emul (checked against the oracle) and by nvcc.
 #pragma once
 #include <stdint.h>
 #include "envelope_core.h"  // CQ_HD, cq_min/cq_max, cq_lowbit/cq_highbit
-#include "sweep_core.h"     // kFarRow, kNoCurH, kNoNxtH, CQ_UNLIKELY
 
 namespace chaq {
+
+constexpr int kFarRow = 1 << 28;  // "no such row"; survives +- image-size arithmetic without overflow
+#define CQ_UNLIKELY(x) __builtin_expect(!!(x), 0)
+
 
 #ifndef CQ_HULL_WIDE
 constexpr int kHullMaxPieceBlocks = 32;  // build runs are at most 1024 rows (int32 range of the domination test)
@@ -123,6 +141,16 @@ struct HullBuild {
     }
 };
 
+// Junctions repaired at the same time (different threads, plain loads and stores on the hull words) must not touch
+// the same WORD. The repair of the junction at row J (a multiple of 32) clears sites in rows [J-2L+1, J+2L-2], i.e.
+// words J/32 - ceil((2L-1)/32) .. J/32 + floor((2L-2)/32); junctions k and k + nphase are pb*nphase words apart.
+// Returns the number of rounds: round i repairs every nphase-th junction starting with the i-th.
+CQ_HD int hull_merge_phases(int L, int pb) {
+    if (L < 1) return 1;
+    const int below = (2 * L - 2) >> 5, above = (2 * L - 1 + 31) >> 5;
+    return (below + above) / pb + 1;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // merge. Ctx provides: uint32_t h_ld(int blk) / void h_st(int blk, uint32_t) (this column's hull words, all
 // blocks of the buffer) and uint32_t g_row(int r).
@@ -201,182 +229,5 @@ struct HullMerge {
     }
 };
 
-
-// ---------------------------------------------------------------------------------------------------------
-// emit. Ctx provides (blk = 32-row block of the buffer; blocks past the buffer read as "no site", class of the
-// last real row):
-//   uint32_t h_ld(int blk)                 this column's finished hull word
-//   uint32_t g_row(int r)
-//   uint32_t cls_fetch(int blk)            class bits of this column for the block's rows (bit j = row 32*blk+j)
-//   uint32_t cls_ld(int slot) / void cls_st(int slot, uint32_t)   ring of kClsRing class words (slot = blk & mask)
-//   int      q_flag(int blk)               0/1: block holds no site in any column of the group and is all class
-//                                          0/1 there; 2: anything else; 3: block outside the buffer
-//   void     out(int cls, int d2c) / void out_run(int cls, int d2c, int n)
-#ifndef CQ_HULL_WIDE
-constexpr int kClsRing = 16;  // class words kept ahead of the row being finished: ceil(L/32) + 2 <= 10
-#else
-constexpr int kClsRing = 64;  // ceil(1024/32) + 2 = 34
-#endif
-
-template <class Ctx>
-struct HullEmit {
-    Ctx& c;
-    int L, C2, reach;
-    int ecls, upd, nb, lastknown;
-    int cur_p, cur_h, nxt_p, nxt_h;
-    int eblk;       // cursor: the sites after nxt (after cur if there is no nxt) are the bits of ehw in block eblk,
-    uint32_t ehw;   // then the blocks after eblk
-    int n0, n1, n2; // blocks of the quiet window with flag 0 / 1 / 2
-    int ev;         // see set_ev
-
-    CQ_HD HullEmit(Ctx& ctx, int lag, int c2) : c(ctx), L(lag), C2(c2), reach((lag + 31) / 32) {}
-
-    CQ_HD uint32_t cls_word(int blk) { return c.cls_ld(blk & (kClsRing - 1)); }
-    // first row in [from, to] whose class differs from cls, or -1 (rows must be in the ring)
-    CQ_HD int cls_up(int from, int to, int cls) {
-        if (from > to) return -1;
-        const uint32_t flip = cls ? 0xFFFFFFFFu : 0u;
-        int b = from >> 5;
-        const int bend = to >> 5;
-        uint32_t bits = (cls_word(b) ^ flip) & (0xFFFFFFFFu << (from & 31));
-        for (;;) {
-            if (b == bend) bits &= (0xFFFFFFFFu >> (31 - (to & 31)));
-            if (bits) return (b << 5) + cq_lowbit(bits);
-            if (b == bend) return -1;
-            ++b;
-            bits = cls_word(b) ^ flip;
-        }
-    }
-    CQ_HD void class_flip(int er) {
-        ecls ^= 1;
-        upd = 1;
-        const int n = cls_up(er + 1, lastknown, ecls);
-        nb = n >= 0 ? n : kFarRow;
-    }
-    // class words of block blk enter the ring; an open-ended run may end there
-    CQ_HD void cls_push(int blk) {
-        const uint32_t w = c.cls_fetch(blk);
-        c.cls_st(blk & (kClsRing - 1), w);
-        lastknown = blk * 32 + 31;
-        if (nb == kFarRow) {
-            const uint32_t x = w ^ (ecls ? 0xFFFFFFFFu : 0u);
-            if (x) { nb = blk * 32 + cq_lowbit(x); ev = cq_min(ev, nb); }
-        }
-    }
-    CQ_HD int height(int r) {
-        const int g = (int)c.g_row(r) + 1;
-        return g * g;
-    }
-    // nxt := the next site of the hull if one is known at a row <= limit or in the block being scanned
-    CQ_HD void next_site(int limit) {
-        for (;;) {
-            if (ehw) {
-                const int j = cq_lowbit(ehw);
-                ehw &= ehw - 1u;
-                nxt_p = eblk * 32 + j;
-                nxt_h = height(nxt_p);
-                return;
-            }
-            if ((eblk + 1) * 32 > limit) { nxt_p = -1; nxt_h = kNoNxtH; return; }
-            ++eblk;
-            ehw = c.h_ld(eblk);
-        }
-    }
-    // ev = the first row at which something other than the plain walk has to happen: the class run ends (nb), the
-    // current site drops out of reach (cur_p + L + 1), or the successor has to be looked up again because a new
-    // block of the hull has come within reach. One compare per row replaces three.
-    CQ_HD void set_ev(int er) {
-        int t = nb;
-        if (cur_p >= 0) t = cq_min(t, cur_p + L + 1);
-        if (nxt_p < 0) t = cq_min(t, ehw != 0u ? er : (eblk + 1) * 32 - L);
-        ev = t;
-    }
-    CQ_HD int advance(int er, int fn) {
-        int fc;
-        do {
-            cur_p = nxt_p; cur_h = nxt_h; fc = fn;
-            next_site(er + L);
-            const int dn = er - nxt_p;
-            fn = dn * dn + nxt_h;
-        } while (fn <= fc);
-        set_ev(er + 1);
-        return fc;
-    }
-    CQ_HD void housekeeping(int er) {
-        if (er == nb) class_flip(er);
-        if (nxt_p < 0 && (ehw != 0u || (eblk + 1) * 32 <= er + L)) next_site(er + L);
-        // a site more than L rows above er no longer matters: move on to the first one within reach
-        const int lowrow = cq_max(er - L, 0);
-        while ((unsigned)cur_p < (unsigned)lowrow) {
-            cur_p = nxt_p; cur_h = nxt_p < 0 ? kNoCurH : nxt_h;
-            if (nxt_p >= 0) next_site(er + L);
-        }
-        set_ev(er + 1);
-    }
-    CQ_HD void emit(int er) {
-        ++upd;
-        if (CQ_UNLIKELY(er >= ev)) housekeeping(er);
-        const int d = er - cur_p;
-        int fc = d * d + cur_h;
-        const int dn = er - nxt_p;
-        const int fn = dn * dn + nxt_h;
-        if (fn <= fc) fc = advance(er, fn);
-        const int v = cq_min(cq_min(upd, nb - er), L + 1);
-        c.out(ecls, cq_min(fc, v * v));
-    }
-    CQ_HD void q_add(int blk, int s) {
-        const int f = c.q_flag(blk);
-        if (f == 0) n0 += s; else if (f == 1) n1 += s; else if (f == 2) n2 += s;
-    }
-
-    // results for buffer rows [y0, y1)
-    CQ_HD void run(int y0, int y1) {
-        const int B0 = y0 >> 5;
-        // class state at y0: the ring gets blocks B0 .. B0+reach, the run's start is looked up above y0
-        nb = 0;  // no open-ended check while the ring fills
-        for (int b = B0; b <= B0 + reach; ++b) cls_push(b);
-        ecls = (int)(cls_word(B0) >> (y0 & 31)) & 1;
-        {
-            const uint32_t flip = ecls ? 0xFFFFFFFFu : 0u;
-            upd = kFarRow;
-            const int blo = cq_max(0, (y0 - L - 1) >> 5);
-            for (int b = B0; b >= blo; --b) {
-                uint32_t x = (b == B0 ? cls_word(b) : c.cls_fetch(b)) ^ flip;
-                if (b == B0) x &= (y0 & 31) ? (0xFFFFFFFFu >> (32 - (y0 & 31))) : 0u;
-                if (x && upd == kFarRow) upd = y0 - (b * 32 + cq_highbit(x)) - 1;  // emit() adds the 1
-            }
-            const int n = cls_up(y0 + 1, lastknown, ecls);
-            nb = n >= 0 ? n : kFarRow;
-        }
-        // hull cursor: nothing taken yet, scanning starts L rows above y0
-        cur_p = -1; cur_h = kNoCurH; nxt_p = -1; nxt_h = kNoNxtH;
-        {
-            const int s = cq_max(y0 - L, 0);
-            eblk = s >> 5;
-            ehw = c.h_ld(eblk) & (0xFFFFFFFFu << (s & 31));
-        }
-        set_ev(y0);
-        // quiet window of block B: blocks B-reach .. B+reach
-        n0 = n1 = n2 = 0;
-        for (int b = B0 - reach; b <= B0 + reach; ++b) q_add(b, 1);
-        for (int B = B0; B * 32 < y1; ++B) {
-            if (B > B0) {
-                cls_push(B + reach);
-                q_add(B + reach, 1);
-                q_add(B - reach - 1, -1);
-            }
-            const int r0 = cq_max(B * 32, y0), r1 = cq_min(B * 32 + 32, y1);
-            if (r1 - r0 == 32 && n2 == 0 && (n0 == 0 || n1 == 0)) {
-                // no site and no class change within reach of any of the 32 rows, in any column of the group
-                ++upd;
-                if (CQ_UNLIKELY(r0 == nb)) { class_flip(r0); set_ev(r0 + 1); }  // only possible for L == 0
-                upd += 31;
-                c.out_run(ecls, C2, 32);
-                continue;
-            }
-            for (int er = r0; er < r1; ++er) emit(er);
-        }
-    }
-};
 
 }  // namespace chaq

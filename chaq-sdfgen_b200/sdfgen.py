@@ -25,7 +25,8 @@ def build_library(force=False):
     return LIB_PATH
 
 
-SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "chaqsdf_profile_enable",
+SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "chaqsdf_reload_tuning",
+           "chaqsdf_profile_enable",
            "chaqsdf_profile_mean_ms", "dist_transform_2d",
            "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_pipeline_plan", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
@@ -47,6 +48,7 @@ def lib():
     L.chaqsdf_launch_count.restype = C.c_ulonglong
     L.chaqsdf_profile_enable.argtypes = [i]
     L.chaqsdf_profile_enable.restype = None
+    L.chaqsdf_reload_tuning.restype = None
     L.chaqsdf_profile_mean_ms.argtypes = [C.POINTER(C.c_float)]
     L.dist_transform_2d.argtypes = [vp, sz, sz]
     L.dist_transform_2d.restype = None
@@ -81,6 +83,11 @@ def launch_count():
     return int(lib().chaqsdf_launch_count())
 
 
+def reload_tuning():
+    """Re-read the CHAQSDF_* tuning switches from the environment (they are otherwise read once, at load)."""
+    lib().chaqsdf_reload_tuning()
+
+
 def profile_enable(on=True):
     """Bracket the kernels of the banded pass 2 with CUDA events (bench.py's roofline)."""
     lib().chaqsdf_profile_enable(int(bool(on)))
@@ -92,7 +99,7 @@ def profile_mean_ms():
     n = lib().chaqsdf_profile_mean_ms(ms)
     if n <= 0:
         raise ChaqSdfError(lib().chaqsdf_last_error_string().decode())
-    return {"hull_build_kernel": float(ms[0]), "hull_merge_par_kernel": float(ms[1]), "hull_emit_kernel": float(ms[2]),
+    return {"hull_build_kernel": float(ms[0]), "hull_merge_par_kernel": float(ms[1]), "hull_paint_kernel": float(ms[2]),
             "calls": int(n)}
 
 

@@ -42,11 +42,16 @@ const char* chaqsdf_last_error_string(void);
 /* Number of kernels this library has launched in this process (all threads); for bench accounting. */
 unsigned long long chaqsdf_launch_count(void);
 
+/* Tuning switches (run lengths, pipeline band heights, CHAQSDF_DT2D ...; csrc/tuning.h lists them) come from the
+ * environment and are read ONCE, when the library is loaded. This re-reads them: a hook for tests and A/B runs. */
+void chaqsdf_reload_tuning(void);
+
 /* Per-kernel timing of the banded pass 2 (spread <= 256), for bench.py's roofline: when enabled, the library
  * brackets its own launches with CUDA events on the caller's stream (the first 64 calls after enabling).
  * chaqsdf_profile_mean_ms waits for them and returns the mean milliseconds of { hull build, junction merge,
- * hull emit } and, as its value, the number of calls averaged (0 with an error string if none). Not thread-safe;
- * leave it off in production (it adds four event records per call). */
+ * hull paint } and, as its value, the number of calls averaged; on any failure (no profiled call, CUDA error) it
+ * returns 0, zeroes ms[] and sets the error string. Not thread-safe; leave it off in production (it adds four
+ * event records per call). */
 void chaqsdf_profile_enable(int on);
 int chaqsdf_profile_mean_ms(float ms[3]);
 
@@ -56,7 +61,7 @@ int chaqsdf_profile_mean_ms(float ms[3]);
  * original it has no return value; on error it leaves img untouched and records the error string.
  *   heights all 0 / +INF (what the CLI passes, sdfgen.c:281,286): exact integer kernels; identical to the stock
  *     build wherever that is exact (sides <= 4098), the exact EDT beyond;
- *   any other height, or CHAQSDF_DT2D=stock in the environment: the reference's float32 envelope restated
+ *   any other height, or CHAQSDF_DT2D=stock in the environment at load time: the reference's float32 envelope restated
  *     operation by operation (csrc/dt_float.cuh), bit-identical to the stock build on square images of any size,
  *     including its inexactness beyond side 4098.
  * Works for non-square images (the original does not: df.c:47, df.c:92). */

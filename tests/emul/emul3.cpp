@@ -1,9 +1,11 @@
-// Host emulation of the build / merge / emit organisation of the banded column pass (hull_core.h) and the level
-// tables (tables.h): the SAME headers the CUDA kernels compile, driven column by column on the CPU, so the logic
-// (piece boundaries, junction repair, cursor walk, quiet blocks) can be checked against the oracle without a GPU.
+// Host emulation of the build / merge / paint organisation of the banded column pass (hull_core.h, paint_core.h)
+// and the level tables (tables.h): the SAME headers the CUDA kernels compile, driven column by column on the CPU, so
+// the logic (run boundaries, junction repair, owner lists, saturated blocks) can be checked against the oracle
+// without a GPU.
 // Test infrastructure only; not part of the product library.
 #include <cstdint>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <vector>
 #include "../../chaq-sdfgen_b200/csrc/tables.h"
@@ -63,12 +65,23 @@ struct BuildCtx : Col {
 };
 
 struct MergeCtx : Col {
+    // junctions of one round run concurrently on the GPU (plain loads and stores): no two of them may store the
+    // same word. writer[b] = junction that stored word b in the current round (-1: none).
+    std::vector<int>* writer = nullptr;
+    int junction_id = -1;
+    long conflicts = 0;
     uint32_t h_ld(int b) { if (b < 0 || b >= nblk) { ++oob; return 0; } return (*H)[b]; }
-    void h_st(int b, uint32_t v) { if (b < 0 || b >= nblk) { ++oob; return; } (*H)[b] = v; }
+    void h_st(int b, uint32_t v) {
+        if (b < 0 || b >= nblk) { ++oob; return; }
+        if (writer) {
+            if ((*writer)[b] >= 0 && (*writer)[b] != junction_id) ++conflicts;
+            (*writer)[b] = junction_id;
+        }
+        (*H)[b] = v;
+    }
 };
 
 struct EmitCtx : Col {
-    uint32_t ring[kClsRing]; int ring_blk[kClsRing];
     int* d2; uint8_t* ocls; int nout = 0;
     uint32_t h_ld(int b) { if (b < 0) { ++oob; return 0; } return b < nblk ? (*H)[b] : 0u; }
     uint32_t cls_fetch(int blk) {
@@ -82,8 +95,6 @@ struct EmitCtx : Col {
     void prefetch_g(int) {}
     long n_live = 0, n_dead = 0;
     bool any(bool b) { if (b) ++n_live; else ++n_dead; return b; }
-    uint32_t cls_ld(int s) { return ring[s]; }
-    void cls_st(int s, uint32_t v) { ring[s] = v; }
     int q_flag(int blk) { return (blk < 0 || blk >= nblk) ? 3 : (*Q)[blk]; }
     void out(int c, int v) { d2[nout] = v; ocls[nout] = (uint8_t)c; ++nout; }
     void out_run(int c, int v, int n) { for (int i = 0; i < n; ++i) out(c, v); }
@@ -93,18 +104,16 @@ struct EmitCtx : Col {
     uint32_t seg_ld(int k) { if (k < 0 || k > 32) { ++oob; return 0; } return seg[k]; }
 };
 
-// 0: HullEmit (row-by-row walk), 1: HullPaint (plan + paint per block). Same inputs, must give the same bytes.
-static int g_emitter = 0;
 static long g_live = 0, g_dead = 0;  // (column, block) pairs painted / skipped as saturated by HullPaint
 extern "C" void emul3_paint_stats(long* live, long* dead) { *live = g_live; *dead = g_dead; g_live = g_dead = 0; }
-extern "C" void emul3_set_emitter(int e) { g_emitter = e; }
 
 // mask: h*w bytes of 0/1. build_blocks: blocks per build run; emit_rows: rows per emit run (0 = whole column);
 // y_begin/y_end: output row range (context rows outside it still exist, as in a row-band buffer).
 // nsub > 1: every build run is built as nsub sub-runs whose junctions are repaired first, looking only at the
 // run's own rows (what one CTA of the build kernel does in shared memory), before the junctions between runs.
-// merge_order 0: junctions top to bottom; 1: in nphase = ceil(4L / run length) rounds, round i taking every
-// nphase-th junction (what the parallel merge kernel amounts to: same-round junctions cannot interact).
+// merge_order 0: junctions top to bottom; 1: in hull_merge_phases(L, run blocks) rounds, round i taking every
+// nphase-th junction (what the parallel merge kernel does; same-round junctions must never store the same hull
+// word -- rc 2500 if they do).
 extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int asym, int build_blocks, int emit_rows,
                          int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order, int nsub) {
     QuantTable q; build_quant_table(spread, asym, &q);
@@ -149,10 +158,17 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
             c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
             HullMerge<MergeCtx> hm(c, L, h);
             if (merge_order == 1) {
-                int nphase = (4 * L + build_blocks * 32 - 1) / (build_blocks * 32);
-                if (nphase < 1) nphase = 1;
-                for (int phase = 0; phase < nphase; ++phase)
-                    for (int k = 1 + phase; k * build_blocks < nblk; k += nphase) hm.junction(k * build_blocks * 32);
+                const int nphase = hull_merge_phases(L, build_blocks);
+                std::vector<int> writer(nblk);
+                c.writer = &writer;
+                for (int phase = 0; phase < nphase; ++phase) {
+                    std::fill(writer.begin(), writer.end(), -1);
+                    for (int k = 1 + phase; k * build_blocks < nblk; k += nphase) {
+                        c.junction_id = k;
+                        hm.junction(k * build_blocks * 32);
+                    }
+                }
+                if (c.conflicts) return 2500;
             } else {
                 for (int b0 = build_blocks; b0 < nblk; b0 += build_blocks) hm.junction(b0 * 32);
             }
@@ -163,14 +179,9 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
             EmitCtx c;
             c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
             c.d2 = cd2.data() + y0; c.ocls = ccls.data() + y0;
-            if (g_emitter == 1) {
-                HullPaint<EmitCtx> hp(c, L, lt.c2);
-                hp.run(y0, y1);
-                g_live += c.n_live; g_dead += c.n_dead;
-            } else {
-                HullEmit<EmitCtx> he(c, L, lt.c2);
-                he.run(y0, y1);
-            }
+            HullPaint<EmitCtx> hp(c, L, lt.c2);
+            hp.run(y0, y1);
+            g_live += c.n_live; g_dead += c.n_dead;
             if (c.nout != y1 - y0) return 2;
             if (c.oob) return 3000;
         }

@@ -111,9 +111,11 @@ def test_band_sizes_do_not_change_the_result(pkg, oracle):
     try:
         for band in ("1", "17", "64", "333", "5000"):
             os.environ["CHAQSDF_BAND_ROWS"] = band
+            pkg.reload_tuning()
             assert np.array_equal(gpu_u8(pkg, img, 1024, 1024, spread=48), want), band
     finally:
         os.environ.pop("CHAQSDF_BAND_ROWS", None)
+        pkg.reload_tuning()
 
 
 def test_strided_input_and_invert(pkg, oracle):
@@ -198,8 +200,10 @@ def test_dist_transform_2d_general_heights(pkg, ref, monkeypatch):
     f = np.where(seeds, np.float32(0), np.float32(np.inf)).astype(np.float32)
     want = ref.dist_transform_2d(f)
     monkeypatch.setenv("CHAQSDF_DT2D", "stock")
+    pkg.reload_tuning()
     got = pkg.dist_transform_2d(f.copy())
     monkeypatch.delenv("CHAQSDF_DT2D")
+    pkg.reload_tuning()
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
 
 
@@ -259,22 +263,34 @@ def test_config4_full_size(pkg, oracle):
 
 
 def test_pass2_organisations_and_run_lengths_agree(pkg, oracle, monkeypatch):
-    """Pass 2 as build/merge/emit with forced run lengths (junction every 32 rows .. one run per column, parallel
-    and sequential junction repair) and as the single sweep: all must give the oracle's bytes."""
+    """Pass 2 with forced run lengths (a junction every 32 rows .. one run per column; junction repair in rounds and
+    sequential; four sub-runs per build CTA): all must give the oracle's bytes. The spread 20 / 24 cases with runs of
+    3 blocks are the ones in which two junctions of one round would share a hull word if rounds were counted in rows
+    instead of words (hull_merge_phases)."""
     rng = np.random.default_rng(77)
     cases = [(oracle.syn_discs(1536), 1536, 1536, 256), (oracle.syn_discs(1024), 1024, 1024, 40),
-             (oracle.syn_noise(700), 700, 700, 9), (random_shapes(rng, 900, 333), 333, 900, 100)]
+             (oracle.syn_noise(700), 700, 700, 9), (random_shapes(rng, 900, 333), 333, 900, 100),
+             (oracle.syn_noise(1100), 1100, 1100, 20), (random_shapes(rng, 1500, 640), 640, 1500, 24),
+             (random_shapes(rng, 2000, 200), 200, 2000, 100)]
     envs = [{}, {"CHAQSDF_HULL_PB": "1", "CHAQSDF_HULL_EB": "1"}, {"CHAQSDF_HULL_PB": "3", "CHAQSDF_HULL_EB": "5"},
             {"CHAQSDF_HULL_PB": "32", "CHAQSDF_HULL_EB": "32"}, {"CHAQSDF_HULL_SEQ": "1", "CHAQSDF_HULL_PB": "2"},
-            {"CHAQSDF_PASS2": "sweep"}, {"CHAQSDF_PASS2": "sweep", "CHAQSDF_SWEEP_SPLIT": "rows"}]
-    for img, w, h, spread in cases:
-        want = oracle.sdf(img, w, h, spread=spread)
-        for env in envs:
-            for k in ("CHAQSDF_HULL_PB", "CHAQSDF_HULL_EB", "CHAQSDF_HULL_SEQ", "CHAQSDF_PASS2", "CHAQSDF_SWEEP_SPLIT"):
-                monkeypatch.delenv(k, raising=False)
-            for k, v in env.items():
-                monkeypatch.setenv(k, v)
-            assert np.array_equal(gpu_u8(pkg, img, w, h, spread=spread), want), (w, h, spread, env)
+            {"CHAQSDF_HULL_PB": "13", "CHAQSDF_HULL_SUB": "1"}, {"CHAQSDF_HULL_PB": "8", "CHAQSDF_HULL_SUB": "4"}]
+    keys = ("CHAQSDF_HULL_PB", "CHAQSDF_HULL_EB", "CHAQSDF_HULL_SEQ", "CHAQSDF_HULL_SUB")
+    try:
+        for img, w, h, spread in cases:
+            want = oracle.sdf(img, w, h, spread=spread)
+            for env in envs:
+                for k in keys:
+                    monkeypatch.delenv(k, raising=False)
+                for k, v in env.items():
+                    monkeypatch.setenv(k, v)
+                pkg.reload_tuning()
+                for rep in range(3 if env.get("CHAQSDF_HULL_PB") == "3" else 1):  # a race would not show every time
+                    assert np.array_equal(gpu_u8(pkg, img, w, h, spread=spread), want), (w, h, spread, env)
+    finally:
+        for k in keys:
+            monkeypatch.delenv(k, raising=False)
+        pkg.reload_tuning()
 
 
 def test_host_api_pipelined_bands(pkg, oracle, monkeypatch):
@@ -285,22 +301,28 @@ def test_host_api_pipelined_bands(pkg, oracle, monkeypatch):
     want = oracle.sdf(img, n, n, spread=spread)
     for rows in ("160", "352", "1000"):
         monkeypatch.setenv("CHAQSDF_PIPE_ROWS", rows)
+        pkg.reload_tuning()
         assert np.array_equal(pkg.sdf_u8(img, n, n, spread=spread), want), rows
     # interleaved (Y,A) input, asymmetric, pinned buffers
     ya = np.ascontiguousarray(np.stack([255 - img, img], axis=-1))
     monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "224")
+    pkg.reload_tuning()
     hin, hout = torch.from_numpy(ya).pin_memory(), torch.empty((n, n), dtype=torch.uint8).pin_memory()
     pkg.sdf_u8(hin, n, n, stride=2, offset=1, spread=spread, asymmetric=True, out=hout)
     assert np.array_equal(hout.numpy(), oracle.sdf(img, n, n, spread=spread, asymmetric=True))
     monkeypatch.delenv("CHAQSDF_PIPE_ROWS")
+    pkg.reload_tuning()
     assert np.array_equal(pkg.sdf_u8(img, n, n, spread=spread), want)
     # repeated calls on alternating images: a stale or early read of the pooled device buffers would show
     flipped = np.ascontiguousarray(img[::-1, ::-1])
     want_f = oracle.sdf(flipped, n, n, spread=spread)
     monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "192")
+    pkg.reload_tuning()
     for rep in range(6):
         src, ref_bytes = (img, want) if rep % 2 == 0 else (flipped, want_f)
         assert np.array_equal(pkg.sdf_u8(src, n, n, spread=spread), ref_bytes), rep
+    monkeypatch.delenv("CHAQSDF_PIPE_ROWS")
+    pkg.reload_tuning()
 
 
 def test_error_paths(pkg):

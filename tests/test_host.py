@@ -205,6 +205,7 @@ def test_host_pipeline_band_schedule(pkg, monkeypatch):
     come first and last, and small images or spreads beyond the banded path are not pipelined."""
     for var in ("CHAQSDF_PIPE_ROWS", "CHAQSDF_PIPE_FIRST"):
         monkeypatch.delenv(var, raising=False)
+    pkg.reload_tuning()
     assert pkg.pipeline_plan(1024, 1024, 1, 64) == []          # < 4 Mpx
     assert pkg.pipeline_plan(16384, 16384, 1, 1024) == []      # general path (spread > 256)
     for (w, h, stride, spread) in [(16384, 16384, 1, 256), (16384, 16384, 2, 256), (4096, 4096, 1, 64), (2048, 2048, 1, 40),
@@ -220,11 +221,15 @@ def test_host_pipeline_band_schedule(pkg, monkeypatch):
     bands = pkg.pipeline_plan(16384, 16384, 1, 256)
     assert len(bands) >= 8 and bands[0] < bands[len(bands) // 2] and bands[-1] < bands[len(bands) // 2], bands
     monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "160")
+    pkg.reload_tuning()
     b = pkg.pipeline_plan(2048, 2048, 1, 40)
     assert sum(b) == 2048 and max(b) <= 160, b                # 2*spread + 64 = 144 <= 160
     monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "64")             # too short for the context: raised to 2*spread + 64
+    pkg.reload_tuning()
     b = pkg.pipeline_plan(2048, 2048, 1, 40)
     assert sum(b) == 2048 and all(x >= 40 + 32 for x in b[:-1]), b
+    monkeypatch.delenv("CHAQSDF_PIPE_ROWS")
+    pkg.reload_tuning()
 
 
 def test_peer_halo_pull_plan_is_paired_and_complete(pkg):
@@ -256,73 +261,7 @@ def test_peer_halo_pull_plan_is_paired_and_complete(pkg):
             assert np.array_equal(bufs[r], np.arange(r0 - ht, r1 + hb)), (h, world, spread, r)
 
 
-# ---------------------------------------------------------------- banded fast path (sweep_core.h), host emulation
-@pytest.fixture(scope="session")
-def emul2(tmp_path_factory):
-    so = str(tmp_path_factory.mktemp("emul2") / "libemul2.so")
-    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-o", so,
-                    os.path.join(ROOT, "tests", "emul", "emul2.cpp")], check=True)
-    L = C.CDLL(so)
-    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
-    L.emul2_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, u8p, C.c_void_p, C.POINTER(C.c_int), C.c_int]
-    return L
-
-
-def _emul2_u8(L, mask, spread, asym, band, gmode=None):
-    """gmode None: run both ring modes (S: g8 in the ring, G: g8 re-read, shorter hull/class rings) and require
-    identical results."""
-    if gmode is None:
-        a, ce = _emul2_u8(L, mask, spread, asym, band, 0)
-        b, _ = _emul2_u8(L, mask, spread, asym, band, 1)
-        assert np.array_equal(a, b), "ring modes S and G disagree"
-        return a, ce
-    h, w = mask.shape
-    out = np.empty((h, w), np.uint8)
-    ce = C.c_int()
-    rc = L.emul2_sdf(np.ascontiguousarray(mask), w, h, spread, int(asym), band, out, None, C.byref(ce), gmode)
-    assert rc == 0, f"emulated banded pass failed (rc={rc}: 1 = cap_eff beyond the build's limit, 2 = row count, >=1000 = stale ring access)"
-    return out, ce.value
-
-
-def test_banded_sweep_matches_oracle_random(emul2, oracle):
-    rng = np.random.default_rng(5)
-    for it in range(150):
-        h, w = int(rng.integers(1, 150)), int(rng.integers(1, 40))
-        dens = rng.choice([0.0, 0.01, 0.05, 0.3, 0.5, 0.9, 1.0])
-        mask = (rng.random((h, w)) < dens).astype(np.uint8)
-        if it % 3 == 0:
-            yy, xx = np.mgrid[0:h, 0:w]
-            mask = np.zeros((h, w), np.uint8)
-            for _ in range(3):
-                cy, cx, r = rng.integers(0, h), rng.integers(0, w), rng.integers(1, 30)
-                mask |= ((yy - cy) ** 2 + (xx - cx) ** 2 <= r * r).astype(np.uint8)
-        img = (mask * 255).astype(np.uint8)
-        for spread in (1, 2, 5, 16, 40, 100, 256):
-            for band in (0, 7, 33, 64):
-                asym = bool(it & 1)
-                got, _ = _emul2_u8(emul2, mask, spread, asym, band)
-                assert np.array_equal(got, oracle.sdf(img, w, h, spread=spread, asymmetric=asym)), (it, h, w, spread, band)
-
-
-def test_banded_sweep_discs_noise_and_cap(emul2, oracle):
-    for n, spread, band in ((384, 16, 0), (384, 64, 100), (384, 256, 0), (1024, 2, 0), (1024, 33, 300), (1024, 256, 400)):
-        img = oracle.syn_discs(n)
-        got, ce = _emul2_u8(emul2, (img > 127).astype(np.uint8), spread, False, band)
-        assert ce <= min(spread + 1, 256)
-        assert np.array_equal(got, oracle.sdf(img, n, n, spread=spread)), (n, spread, band)
-    noise = oracle.syn_noise(300)
-    got, _ = _emul2_u8(emul2, (noise > 127).astype(np.uint8), 8, True, 50)
-    assert np.array_equal(got, oracle.sdf(noise, 300, 300, spread=8, asymmetric=True))
-    # the largest spread of the banded path must still fit 8 bits, symmetric and asymmetric
-    tall = np.zeros((700, 9), np.uint8)
-    tall[300:340, 2:6] = 1
-    for asym in (False, True):
-        got, ce = _emul2_u8(emul2, tall, 256, asym, 0)
-        assert ce == 256
-        assert np.array_equal(got, oracle.sdf(tall * 255, 9, 700, spread=256, asymmetric=asym))
-
-
-# ---------------------------------------------------------------- build / merge / emit (hull_core.h), host emulation
+# ---------------------------------------------------------------- build / merge / paint (hull_core.h, paint_core.h), host emulation
 def _build_emul3(tmp_path_factory, name, *defines):
     so = str(tmp_path_factory.mktemp(name) / f"lib{name}.so")
     subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", *defines, "-o", so,
@@ -366,7 +305,7 @@ def _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0=0, y1=None, ord
     return out, ce.value
 
 
-def test_hull_build_merge_emit_matches_oracle_random(emul3, oracle):
+def test_hull_build_merge_paint_matches_oracle_random(emul3, oracle):
     """Run lengths from one block (a junction every 32 rows, far shorter than the reach) to 32 blocks."""
     rng = np.random.default_rng(5)
     for it in range(100):
@@ -403,6 +342,30 @@ def test_hull_discs_noise_and_row_ranges(emul3, oracle):
     want = oracle.sdf(img, 512, 512, spread=40)
     got, _ = _emul3_u8(emul3, (img > 127).astype(np.uint8), 40, False, 4, 96, 100, 333)
     assert np.array_equal(got[100:333], want[100:333])
+
+
+def test_hull_merge_rounds_never_share_a_hull_word(emul3, oracle):
+    """Junctions repaired in the same round run concurrently on the GPU with plain loads and stores, so two of them
+    must never store the same 32-row hull word. Counting rounds in rows (ceil(4L / run length)) allowed exactly that
+    for 2L mod 32 in 2..16 with short runs (spread 17..24 with runs of 3 blocks, spread ~100 with 13); rounds are
+    counted in words now (hull_merge_phases). The emulation fails with rc 2500 when two same-round junctions store one
+    word; dense glyph-like data makes the repairs reach as far as they can."""
+    rng = np.random.default_rng(21)
+    h, w = 1500, 6
+    masks = [(rng.random((h, w)) < 0.5).astype(np.uint8), (rng.random((h, w)) < 0.03).astype(np.uint8)]
+    yy, xx = np.mgrid[0:h, 0:w]
+    m = np.zeros((h, w), np.uint8)
+    for _ in range(40):
+        cy, cx, r = rng.integers(0, h), rng.integers(-30, w + 30), rng.integers(2, 40)
+        m |= ((yy - cy) ** 2 + (xx - cx) ** 2 <= r * r).astype(np.uint8)
+    masks.append(m)
+    for mask in masks:
+        img = (mask * 255).astype(np.uint8)
+        for spread, bbs in ((17, (3, 1, 2)), (20, (3, 5)), (24, (3, 4)), (100, (13, 7)), (256, (16, 17, 31)), (1, (1,)), (8, (1, 2))):
+            want = oracle.sdf(img, w, h, spread=spread)
+            for bb in bbs:
+                got, _ = _emul3_u8(emul3, mask, spread, False, bb, 0, order=1)
+                assert np.array_equal(got, want), (spread, bb)
 
 
 def test_hull_wide_variant_matches_oracle_beyond_the_banded_spreads(emul3_wide, oracle):
