@@ -73,6 +73,51 @@ def syn_discs(n, seed=88172645463325252, n_discs=200, rows=None):
     return img
 
 
+def syn_glyphs(count, n=256, first=0):
+    """SYN-GLYPH(first .. first+count-1) of SURVEY.md 8(d) as one [count, n, n] array: xorshift64 seeded with
+    base + index, union of 2-5 strokes (annuli and thick segments, 6-20 px wide) >= 16 px from the border. The same
+    integer arithmetic as oracle_syn_glyph (oracle/edt_oracle.c); tests/test_host.py checks that the two agree."""
+    M = (1 << 64) - 1
+    yy, xx = np.mgrid[0:n, 0:n].astype(np.int64)
+    imgs = np.zeros((count, n, n), np.uint8)
+    for g in range(count):
+        s = (88172645463325252 + first + g) & M
+
+        def rnd():
+            nonlocal s
+            s ^= (s << 13) & M
+            s ^= s >> 7
+            s ^= (s << 17) & M
+            return s
+
+        img = imgs[g]
+        for _ in range(2 + rnd() % 4):
+            kind = rnd() % 2
+            wd = 6 + rnd() % 15
+            if kind == 0:
+                R = 24 + rnd() % (n // 2 - 40)
+                span = n - 32 - 2 * R
+                cx = 16 + R + rnd() % span
+                cy = 16 + R + rnd() % span
+                inner = max(R - wd, 0)
+                d2 = (xx - cx) ** 2 + (yy - cy) ** 2
+                img[(d2 <= R * R) & (d2 >= inner * inner)] = 255
+            else:
+                hw = wd // 2
+                span = n - 32 - 2 * hw
+                x0, y0 = 16 + hw + rnd() % span, 16 + hw + rnd() % span
+                x1, y1 = 16 + hw + rnd() % span, 16 + hw + rnd() % span
+                dx, dy = x1 - x0, y1 - y0
+                L2 = dx * dx + dy * dy
+                px, py = xx - x0, yy - y0
+                t = px * dx + py * dy
+                c = px * dy - py * dx
+                hit = np.where(t <= 0, px * px + py * py <= hw * hw,
+                               np.where(t >= L2, (xx - x1) ** 2 + (yy - y1) ** 2 <= hw * hw, c * c <= hw * hw * L2))
+                img[hit] = 255
+    return imgs
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"

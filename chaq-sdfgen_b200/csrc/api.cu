@@ -18,6 +18,7 @@
 #include "rowscan8.cuh"
 #include "hull.cuh"
 #include "paint.cuh"
+#include "glyph.cuh"
 #include "tuning.h"
 
 using namespace chaq;
@@ -76,6 +77,7 @@ struct Tables {
     QuantTable* dq = nullptr;   // device copies
     LevelTable* dl = nullptr;
     LevelTable hl;              // host copy (cap_eff decides the geometry of the banded path)
+    uint8_t* dlut = nullptr;    // cap_eff <= kGlyphMaxC: byte for (class, clamped D2), for the fused small-image kernel
 };
 std::map<std::tuple<int, size_t, int>, Tables> g_tables;
 
@@ -111,6 +113,16 @@ int get_table(size_t spread, int asymmetric, const Tables** out) {
         CQ_CUDA(cudaMemcpy(t.dq, &h, sizeof(QuantTable), cudaMemcpyHostToDevice));
         CQ_CUDA(cudaMalloc(&t.dl, sizeof(LevelTable)));
         CQ_CUDA(cudaMemcpy(t.dl, &t.hl, sizeof(LevelTable), cudaMemcpyHostToDevice));
+        if (t.hl.cap_eff <= kGlyphMaxC) {
+            std::string lut((size_t)2 * kGlyphLutStride, '\0');
+            for (int cls = 0; cls < 2; ++cls)
+                for (int d2 = 0; d2 <= t.hl.c2; ++d2) {
+                    const int m = level_of(t.hl.thr[cls], d2);
+                    lut[(size_t)cls * kGlyphLutStride + d2] = (char)(uint8_t)(cls ? m : 255 - m);
+                }
+            CQ_CUDA(cudaMalloc(&t.dlut, lut.size()));
+            CQ_CUDA(cudaMemcpy(t.dlut, lut.data(), lut.size(), cudaMemcpyHostToDevice));
+        }
         it = g_tables.emplace(key, t).first;
     }
     *out = &it->second;
@@ -249,6 +261,45 @@ int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, 
     rowscan8_kernel<<<blocks, kRow8Warps * 32, smem, st>>>(rp);
     CQ_LAUNCHED("rowscan8_kernel", blocks, smem);
     return CHAQSDF_OK;
+}
+
+// ---- fused small-image path (glyph.cuh) -----------------------------------------------------------------------
+// Does the batch go through one CTA per image? Needs: byte-contiguous pixels, width a multiple of 32 up to 256,
+// C <= 33, and the image's planes in shared memory.
+int glyph_lmax(int L) { return L <= 8 ? 8 : (L <= 16 ? 16 : 32); }
+bool glyph_fits(size_t w, size_t h, size_t stride, const Tables* tab, const DevInfo& di) {
+    if (g_tuning.glyph == 1) return false;
+    if (stride != 1 || w % 32 != 0 || w > 256 || w < 32 || h < 1 || h > 1024 || !tab->dlut) return false;
+    if (tab->hl.cap_eff > kGlyphMaxC) return false;
+    return glyph_smem((int)w, (int)h, glyph_lmax(tab->hl.cap_eff - 1)) <= (size_t)di.max_smem_optin;
+}
+template <int LMAX>
+int launch_glyph_t(const GlyphParams& p, size_t smem, cudaStream_t st) {
+    static int raised[64] = {0};
+    int dev = 0;
+    CQ_CUDA(cudaGetDevice(&dev));
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (dev < 64 && (int)smem > raised[dev]) {
+            CQ_CUDA(cudaFuncSetAttribute(glyph_kernel<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            raised[dev] = (int)smem;
+        }
+    }
+    glyph_kernel<LMAX><<<(unsigned)p.n, kGlyphThreads, smem, st>>>(p);
+    CQ_LAUNCHED("glyph_kernel", p.n, smem);
+    return CHAQSDF_OK;
+}
+int launch_glyph(const uint8_t* d_imgs, size_t n, size_t w, size_t h, int test_above, const Tables* tab, uint8_t* d_out,
+                 cudaStream_t st) {
+    GlyphParams p{};
+    p.img = d_imgs; p.out = d_out; p.lut = tab->dlut;
+    p.w = (int)w; p.h = (int)h; p.n = (int)n; p.wq = (int)(w / 32); p.hb = (int)((h + 31) / 32);
+    p.C = tab->hl.cap_eff; p.C2 = tab->hl.c2; p.above = test_above ? 1 : 0;
+    const int lmax = glyph_lmax(p.C - 1);
+    const size_t smem = glyph_smem(p.w, p.h, lmax);
+    if (lmax == 8) return launch_glyph_t<8>(p, smem, st);
+    if (lmax == 16) return launch_glyph_t<16>(p, smem, st);
+    return launch_glyph_t<32>(p, smem, st);
 }
 
 // optional per-kernel timing (chaqsdf_profile_enable): events around the launches of the banded pass 2
@@ -460,6 +511,11 @@ int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t 
     cudaStream_t st = (cudaStream_t)stream;
     if (banded(spread)) {
         if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
+        DevInfo di;
+        if (int rc = device_info(&di)) return rc;
+        // batches of small images with a small spread: one CTA per image, nothing but the bytes in and out touches HBM
+        if (n <= 0x7fffffff && (n >= 2 || g_tuning.glyph == 2) && glyph_fits(w, h, stride, tab, di))
+            return launch_glyph(d_imgs, n, w, h, test_above, tab, d_out, st);
         const size_t inter_bytes = align_up(n * h * banded_rs(w), 256);
         if (workspace_bytes < inter_bytes + hull_ws_bytes(n, w, h)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
         if (int rc = launch_rowscan8(d_imgs, w, n * h, stride, offset, test_above, spread, (uint8_t*)d_workspace, st)) return rc;

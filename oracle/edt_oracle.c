@@ -251,3 +251,46 @@ void oracle_syn_noise(uint8_t* img, size_t w, size_t h, uint64_t seed) {
     uint64_t s = seed ? seed : 88172645463325252ULL;
     for (size_t i = 0; i < w * h; ++i) img[i] = ((xs64(&s) & 63) == 0) ? 255 : 0;
 }
+
+/* SYN-GLYPH(i) of SURVEY.md section 8(d): an n x n canvas (n >= 96), xorshift64 seeded with base + i, union of 2-5
+ * strokes -- annuli and thick segments, 6-20 px wide -- kept >= 16 px from the border. Integer arithmetic only, so
+ * bench.py's numpy restatement reproduces it bit for bit. */
+void oracle_syn_glyph(uint8_t* img, size_t n, uint64_t index) {
+    uint64_t s = 88172645463325252ULL + index;
+    const int64_t N = (int64_t)n;
+    memset(img, 0, n * n);
+    int k = 2 + (int)(xs64(&s) % 4);
+    for (int st = 0; st < k; ++st) {
+        int type = (int)(xs64(&s) % 2);
+        int64_t wd = 6 + (int64_t)(xs64(&s) % 15);
+        if (type == 0) {
+            int64_t R = 24 + (int64_t)(xs64(&s) % (uint64_t)(N / 2 - 40));
+            int64_t span = N - 32 - 2 * R;
+            int64_t cx = 16 + R + (int64_t)(xs64(&s) % (uint64_t)span);
+            int64_t cy = 16 + R + (int64_t)(xs64(&s) % (uint64_t)span);
+            int64_t inner = R - wd > 0 ? R - wd : 0;
+            for (int64_t y = cy - R; y <= cy + R; ++y)
+                for (int64_t x = cx - R; x <= cx + R; ++x) {
+                    int64_t d2 = (x - cx) * (x - cx) + (y - cy) * (y - cy);
+                    if (d2 <= R * R && d2 >= inner * inner) img[(size_t)y * n + (size_t)x] = 255;
+                }
+        } else {
+            int64_t hw = wd / 2;
+            int64_t span = N - 32 - 2 * hw;
+            int64_t x0 = 16 + hw + (int64_t)(xs64(&s) % (uint64_t)span), y0 = 16 + hw + (int64_t)(xs64(&s) % (uint64_t)span);
+            int64_t x1 = 16 + hw + (int64_t)(xs64(&s) % (uint64_t)span), y1 = 16 + hw + (int64_t)(xs64(&s) % (uint64_t)span);
+            int64_t dx = x1 - x0, dy = y1 - y0, L2 = dx * dx + dy * dy;
+            int64_t xa = (x0 < x1 ? x0 : x1) - hw, xb = (x0 > x1 ? x0 : x1) + hw;
+            int64_t ya = (y0 < y1 ? y0 : y1) - hw, yb = (y0 > y1 ? y0 : y1) + hw;
+            for (int64_t y = ya; y <= yb; ++y)
+                for (int64_t x = xa; x <= xb; ++x) {
+                    int64_t px = x - x0, py = y - y0, t = px * dx + py * dy;
+                    int hit;
+                    if (t <= 0) hit = px * px + py * py <= hw * hw;
+                    else if (t >= L2) hit = (x - x1) * (x - x1) + (y - y1) * (y - y1) <= hw * hw;
+                    else { int64_t c = px * dy - py * dx; hit = c * c <= hw * hw * L2; }
+                    if (hit) img[(size_t)y * n + (size_t)x] = 255;
+                }
+        }
+    }
+}

@@ -53,6 +53,7 @@ class Oracle:
         L.oracle_dist_transform_2d_binary.restype = C.c_int
         L.oracle_syn_discs.argtypes = [_u8p, C.c_size_t, C.c_size_t, C.c_uint64, C.c_int]
         L.oracle_syn_noise.argtypes = [_u8p, C.c_size_t, C.c_size_t, C.c_uint64]
+        L.oracle_syn_glyph.argtypes = [_u8p, C.c_size_t, C.c_uint64]
         L.oracle_signed_from_d2.argtypes = [C.c_int32, C.c_int32]
         L.oracle_signed_from_d2.restype = C.c_float
         L.oracle_byte_from_signed.argtypes = [C.c_float, C.c_size_t, C.c_int]
@@ -102,6 +103,13 @@ class Oracle:
         img = np.empty((h, w), np.uint8)
         self.L.oracle_syn_discs(img.reshape(-1), w, h, seed, n_discs)
         return img
+
+    def syn_glyphs(self, count, n=256, first=0):
+        """SYN-GLYPH(first) .. SYN-GLYPH(first + count - 1) as one [count, n, n] array."""
+        imgs = np.empty((count, n, n), np.uint8)
+        for i in range(count):
+            self.L.oracle_syn_glyph(imgs[i].reshape(-1), n, first + i)
+        return imgs
 
     def syn_noise(self, w, h=None, seed=0):
         h = w if h is None else h

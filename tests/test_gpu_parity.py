@@ -219,6 +219,65 @@ def test_batched_glyphs(pkg, oracle):
         assert np.array_equal(got[k], oracle.sdf(imgs[k], s, s, spread=16)), k
 
 
+def _batched(pkg, imgs, **kw):
+    n, h, w = imgs.shape
+    d = torch.from_numpy(np.ascontiguousarray(imgs)).cuda()
+    out = pkg.sdf_u8_batched_device(d, n, w, h, **kw)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def test_fused_small_image_kernel(pkg, oracle, monkeypatch):
+    """Batches of small images with spread <= 32 go through glyph_kernel (one CTA per image, both passes in shared
+    memory). Every window size of the kernel (L <= 8 / 16 / 32), both threshold directions, asymmetric, ragged heights,
+    every width it takes, and a single image forced through it; each image against the oracle, and the general
+    two-pass path (CHAQSDF_GLYPH=never) must agree byte for byte."""
+    rng = np.random.default_rng(31)
+    before = pkg.launch_count()
+    cases = [(5, 32, 32, 4, {}), (9, 64, 100, 8, {"asymmetric": True}), (7, 256, 33, 16, {}), (6, 128, 128, 32, {}),
+             (4, 96, 70, 16, {"test_above": False}), (3, 256, 256, 32, {"asymmetric": True}), (2, 160, 1, 3, {}),
+             (8, 224, 75, 1, {}), (3, 256, 300, 20, {})]
+    for (n, w, h, spread, kw) in cases:
+        imgs = np.stack([random_shapes(rng, h, w) if k % 3 else (rng.random((h, w)) < 0.5).astype(np.uint8) * 255
+                         for k in range(n)])
+        if n > 2:
+            imgs[0][:] = 0
+        if n > 3:
+            imgs[1][:] = 255
+            imgs[2][h // 2, w // 2] ^= 255
+        got = _batched(pkg, imgs, spread=spread, **kw)
+        for k in range(n):
+            assert np.array_equal(got[k], oracle.sdf(imgs[k], w, h, spread=spread, **kw)), (n, w, h, spread, kw, k)
+        monkeypatch.setenv("CHAQSDF_GLYPH", "never")
+        pkg.reload_tuning()
+        two_pass = _batched(pkg, imgs, spread=spread, **kw)
+        monkeypatch.delenv("CHAQSDF_GLYPH")
+        pkg.reload_tuning()
+        assert np.array_equal(got, two_pass), (n, w, h, spread)
+    # the fused kernel is one launch per batch: 9 batches fused + 9 x (pass 1 + build + paint [+ merges]) unfused
+    assert pkg.launch_count() - before >= 9 + 9 * 3
+    # one image, forced
+    img = random_shapes(rng, 256, 256)
+    monkeypatch.setenv("CHAQSDF_GLYPH", "always")
+    pkg.reload_tuning()
+    l0 = pkg.launch_count()
+    got = gpu_u8(pkg, img, 256, 256, spread=16)
+    assert pkg.launch_count() - l0 == 1
+    monkeypatch.delenv("CHAQSDF_GLYPH")
+    pkg.reload_tuning()
+    assert np.array_equal(got, oracle.sdf(img, 256, 256, spread=16))
+
+
+def test_config3_at_its_shape(pkg, oracle):
+    """BASELINE config 3: 4096 glyphs of 256 x 256 (SYN-GLYPH of SURVEY.md 8(d), oracle/edt_oracle.c), spread 16, one
+    batched call; every glyph against the oracle."""
+    n, s, spread = 4096, 256, 16
+    imgs = oracle.syn_glyphs(n, s)
+    got = _batched(pkg, imgs, spread=spread)
+    bad = [k for k in range(n) if not np.array_equal(got[k], oracle.sdf(imgs[k], s, s, spread=spread))]
+    assert not bad, f"{len(bad)} glyphs differ, first {bad[:5]}"
+
+
 def test_row_band_sharding_single_process(pkg, oracle):
     """The multi-GPU decomposition, emulated on one GPU: each 'rank' runs pass 1 on its band, halos are copied
     as exchange_halos would, pass 2 runs per band; the stitched result must equal the unsharded one."""

@@ -232,6 +232,17 @@ def test_host_pipeline_band_schedule(pkg, monkeypatch):
     pkg.reload_tuning()
 
 
+def test_syn_glyph_generators_agree(oracle):
+    """SYN-GLYPH exists twice (C in the oracle for the tests, numpy in bench.py for the GPU box): same bytes."""
+    import bench
+    for n, first, count in ((256, 0, 12), (256, 4090, 6), (128, 3, 5), (96, 0, 4)):
+        a, b = oracle.syn_glyphs(count, n, first), bench.syn_glyphs(count, n, first)
+        assert np.array_equal(a, b), (n, first)
+        assert not a[:, :16].any() and not a[:, -16:].any() and not a[:, :, :16].any() and not a[:, :, -16:].any()
+    cov = (oracle.syn_glyphs(64) > 0).mean()
+    assert 0.05 < cov < 0.5
+
+
 def test_peer_halo_pull_plan_is_paired_and_complete(pkg):
     """The peer-memory exchange (pull_halos) on paper: every signal has exactly one waiter, only owned rows are read,
     and after the copies every rank's buffer holds image rows [r0 - halo_top, r1 + halo_bot) in order -- including
