@@ -98,8 +98,9 @@ __global__ void __launch_bounds__(kGlyphThreads, 2) glyph_kernel(GlyphParams p) 
                 const uint32_t flip = ((word >> b) & 1u) ? 0xFFFFFFFFu : 0u;
                 const uint32_t R = __funnelshift_rc(word, wnext, b + 1) ^ flip;    // bit 0 = pixel x+1
                 const uint32_t Lw = __funnelshift_lc(wprev, word, 32 - b) ^ flip; // bit 31 = pixel x-1
-                const int dr = R ? __ffs((int)R) : 64;
-                const int dl = Lw ? __clz((int)Lw) + 1 : 64;
+                // 33 (> any reach) when the window holds no change: clz(0) = 32
+                const int dr = __clz((int)__brev(R)) + 1;
+                const int dl = __clz((int)Lw) + 1;
                 const int g = min(min(dl, dr), C);
                 if (i == 0 || i == 4) packed[i >> 2] = 0u;
                 packed[i >> 2] |= (uint32_t)g << (8 * (i & 3));
@@ -149,18 +150,39 @@ __global__ void __launch_bounds__(kGlyphThreads, 2) glyph_kernel(GlyphParams p) 
         const uint32_t cup = s_clsT[(size_t)m * w + x], cdn = s_clsT[(size_t)(m + 2) * w + x];
         uint8_t* o = out + (size_t)(32 * m) * w + x;
         const int jn = min(32, h - 32 * m);
+        // no class change in this column within 32 rows of the block, for every column of the warp: V is out of reach
+        const bool vflat = cw == cup && cw == cdn && (cw == 0u || cw == 0xFFFFFFFFu);
+        if (__all_sync(0xffffffffu, vflat)) {
+            const uint8_t* lut = s_lut + (cw & 1u) * kGlyphLutStride;
+            uint32_t any = 0u;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            if (j < jn) {
-                const uint32_t cls = (cw >> j) & 1u;
-                const uint32_t flip = cls ? 0xFFFFFFFFu : 0u;
-                const uint32_t U = __funnelshift_lc(cup, cw, 32 - j) ^ flip;  // bit 31 = row y-1
-                const uint32_t D = __funnelshift_rc(cw, cdn, j + 1) ^ flip;    // bit 0 = row y+1
-                const int du = U ? __clz((int)U) + 1 : 64;
-                const int dd = D ? __ffs((int)D) : 64;
-                const uint32_t v = (uint32_t)min(du, dd);
-                const uint32_t d2 = min((acc[j >> 1] >> (16 * (j & 1))) & 0xFFFFu, v * v);  // acc never exceeds C^2
-                o[(size_t)j * w] = s_lut[cls * kGlyphLutStride + d2];
+            for (int i = 0; i < 16; ++i) any |= acc[i] ^ (c2 | (c2 << 16));
+            if (__all_sync(0xffffffffu, any == 0u)) {
+                // nothing within reach of any pixel of the 32 x 32 block: one saturated byte per column
+                const uint8_t b = lut[c2];
+                for (int j = 0; j < jn; ++j, o += w) *o = b;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    if (j < jn) {
+                        *o = lut[(acc[j >> 1] >> (16 * (j & 1))) & 0xFFFFu];
+                        o += w;
+                    }
+                }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (j < jn) {
+                    const uint32_t cls = (cw >> j) & 1u;
+                    const uint32_t flip = 0u - cls;
+                    const uint32_t U = __funnelshift_lc(cup, cw, 32 - j) ^ flip;  // bit 31 = row y-1
+                    const uint32_t D = __funnelshift_rc(cw, cdn, j + 1) ^ flip;   // bit 0 = row y+1
+                    const uint32_t v = (uint32_t)min(__clz((int)U), __clz((int)__brev(D))) + 1u;  // 33 if none in the window
+                    const uint32_t d2 = min((acc[j >> 1] >> (16 * (j & 1))) & 0xFFFFu, v * v);  // acc never exceeds C^2
+                    *o = (cls ? s_lut + kGlyphLutStride : s_lut)[d2];
+                    o += w;
+                }
             }
         }
     }
