@@ -28,7 +28,8 @@ def build(force=False):
     if not need and os.path.getmtime(src) > os.path.getmtime(lib):
         need = True
     if need or (os.path.exists("/root/reference/openmp/df.c")
-                and not os.path.exists(os.path.join(HERE, "_ref", "libchaqref.so"))):
+                and not (os.path.exists(os.path.join(HERE, "_ref", "libchaqref.so"))
+                         and os.path.exists(os.path.join(HERE, "_ref", "libchaqref_dbl.so")))):
         subprocess.run(["make", "-C", HERE, "-s"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
 
 
@@ -121,9 +122,10 @@ class Oracle:
 class Ref:
     """The stock reference build. Square images only; exact only for side <= 4098."""
 
-    def __init__(self):
+    def __init__(self, variant=""):
+        """variant "": the unmodified build; "_dbl": parabola_intersect in double (oracle/Makefile), exact at any size."""
         build()
-        path = os.path.join(HERE, "_ref", "libchaqref.so")
+        path = os.path.join(HERE, "_ref", f"libchaqref{variant}.so")
         if not os.path.exists(path):
             raise FileNotFoundError(path)
         L = C.CDLL(path)

@@ -321,6 +321,91 @@ def test_config4_full_size(pkg, oracle):
     assert np.array_equal(gt, want.T)
 
 
+def test_large_spread_instances(pkg, oracle):
+    """Spreads beyond the banded path (> 256), including BASELINE config 5's spread 1024 on enough rows (>= 2304) that
+    its own pass-2 instance runs, on shapes and on noise, symmetric and asymmetric."""
+    rng = np.random.default_rng(41)
+    w, h = 1536, 2560
+    discs = oracle.syn_discs(w, h)
+    noise = (rng.random((h, w)) < 1 / 3000).astype(np.uint8) * 255
+    for img in (discs, noise):
+        for spread, asym in ((1024, False), (1024, True), (300, False), (700, True)):
+            got = gpu_u8(pkg, img, w, h, spread=spread, asymmetric=asym)
+            assert np.array_equal(got, oracle.sdf(img, w, h, spread=spread, asymmetric=asym)), (spread, asym)
+    tall = np.zeros((5000, 96), np.uint8)
+    tall[2400:2600, 30:60] = 255
+    assert np.array_equal(gpu_u8(pkg, tall, 96, 5000, spread=2000), oracle.sdf(tall, 96, 5000, spread=2000))
+
+
+def test_unwindowed_paths_on_tall_images(pkg, oracle, ref):
+    """The exact-fields entry and the df.h drop-in on images of >= 3072 rows (where the column state no longer fits
+    shared memory and lives in the workspace), and a spread larger than the image on that many rows."""
+    rng = np.random.default_rng(43)
+    n = 3200
+    img = random_shapes(rng, n, n)
+    res = pkg.sdf_fields_device(torch.from_numpy(img).cuda(), n, n, spread=64)
+    torch.cuda.synchronize()
+    out, sdf, din, dout = oracle.sdf(img, n, n, spread=64, fields=True)
+    assert np.array_equal(res["d2_in"].cpu().numpy(), din) and np.array_equal(res["d2_out"].cpu().numpy(), dout)
+    assert np.array_equal(res["out"].cpu().numpy(), out)
+    assert np.array_equal(res["sdf"].cpu().numpy().view(np.uint32), sdf.view(np.uint32))
+    del res
+    assert np.array_equal(gpu_u8(pkg, img, n, n, spread=5000), oracle.sdf(img, n, n, spread=5000))
+    n = 4096  # the largest side at which the stock build is exact: 0 ulp against it
+    seeds = rng.random((n, n)) < 0.00005
+    f = np.where(seeds, np.float32(0), np.float32(np.inf)).astype(np.float32)
+    got = pkg.dist_transform_2d(f.copy())
+    assert np.array_equal(got.view(np.uint32), ref.dist_transform_2d(f).view(np.uint32))
+
+
+def test_config5_at_its_shape_band_wise(pkg, oracle):
+    """BASELINE config 5 (SYN-DISCS(32768), spread 1024) on one GPU, checked against the oracle band by band: the
+    oracle runs on each band plus 1024 context rows (exact for the band's rows: nothing farther away can change a byte).
+    Bands at the top edge, in the middle and at the bottom edge."""
+    n, spread = 32768, 1024
+    img = oracle.syn_discs(n)
+    d = torch.from_numpy(img).cuda()
+    out = pkg.sdf_u8_device(d, n, n, spread=spread)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    del d, out
+    for (a, b) in ((0, 384), (15000, 15384), (24001, 24300), (n - 384, n)):
+        lo, hi = max(0, a - spread - 1), min(n, b + spread + 1)
+        want = oracle.sdf(img[lo:hi], n, hi - lo, spread=spread)[a - lo:b - lo]
+        assert np.array_equal(got[a:b], want), (a, b)
+
+
+def test_two_host_threads(pkg, oracle):
+    """dist_transform_2d is called from two OpenMP section threads at once by the reference's main (sdfgen.c:277-289);
+    chaqsdf_u8 may be too. Two threads, different inputs, many rounds: every result must be the single-threaded one."""
+    import threading
+    rng = np.random.default_rng(47)
+    n = 700
+    fields = [np.where(rng.random((n, n)) < p, np.float32(0), np.float32(np.inf)).astype(np.float32) for p in (0.001, 0.01)]
+    want_f = [oracle.dist_transform_2d_binary(f) for f in fields]
+    imgs = [random_shapes(rng, 1100, 900), oracle.syn_discs(900, 1100)]
+    want_b = [oracle.sdf(im, 900, 1100, spread=48) for im in imgs]
+    errors = []
+
+    def work(k):
+        try:
+            for rep in range(12):
+                got = pkg.dist_transform_2d(fields[k].copy())
+                if not np.array_equal(got.view(np.uint32), want_f[k].view(np.uint32)):
+                    errors.append(("dist_transform_2d", k, rep))
+                if not np.array_equal(pkg.sdf_u8(imgs[k], 900, 1100, spread=48), want_b[k]):
+                    errors.append(("sdf_u8", k, rep))
+        except Exception as e:  # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errors, errors[:5]
+
+
 def test_pass2_organisations_and_run_lengths_agree(pkg, oracle, monkeypatch):
     """Pass 2 with forced run lengths (a junction every 32 rows .. one run per column; junction repair in rounds and
     sequential; four sub-runs per build CTA): all must give the oracle's bytes. The spread 20 / 24 cases with runs of

@@ -90,3 +90,26 @@ def test_synthetic_generators_are_deterministic(oracle):
     assert 0.2 < (a > 127).mean() < 0.9
     b = oracle.syn_noise(256)
     assert abs((b > 127).mean() - 1 / 64) < 0.01
+
+
+def test_oracle_pinned_above_side_4098_by_the_double_intersect_build(oracle):
+    """Beyond side 4098 the stock float32 build is itself inexact, so it cannot pin the
+    oracle there. oracle/_ref/libchaqref_dbl.so is the reference with ONE line changed in a throw-away copy:
+    parabola_intersect (df.c:9-15) evaluated in double (oracle/Makefile). It must equal the exact integer oracle byte
+    for byte, while the stock build differs in about 6 % of the bytes at 8192^2, by at most 3 grey levels (the numbers
+    SURVEY.md 8(c) predicts; profiles/r02_stock_mismatch.json has 16384^2 as well)."""
+    from oracle import Ref
+    if not os.path.exists(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "_ref", "libchaqref_dbl.so")):
+        pytest.skip("oracle/_ref/libchaqref_dbl.so not built (needs the reference tree)")
+    dbl, stock = Ref("_dbl"), Ref()
+    n, spread = 8192, 64
+    img = oracle.syn_discs(n)
+    exact = oracle.sdf(img, n, n, spread=spread)
+    assert np.array_equal(dbl.sdf_u8(img, n, n, spread=spread), exact)
+    d = stock.sdf_u8(img, n, n, spread=spread).astype(np.int16) - exact
+    assert 0.05 < (d != 0).mean() < 0.07 and np.abs(d).max() <= 3
+    n = 5000
+    noise = (np.random.default_rng(3).random((n, n)) < 1 / 200).astype(np.uint8) * 255
+    for asym in (False, True):
+        assert np.array_equal(dbl.sdf_u8(noise, n, n, spread=300, asymmetric=asym),
+                              oracle.sdf(noise, n, n, spread=300, asymmetric=asym))
