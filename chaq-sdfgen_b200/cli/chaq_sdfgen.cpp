@@ -10,14 +10,18 @@
 //   * output type: -f wins, else the three characters after the last '.' of the output name compared to
 //     png bmp jpg tga, else PNG;  the result is a 1-channel 8-bit image;
 //   * the image is decoded to (luminance, alpha) pairs; the alpha channel is tested unless -l is given.
-// Added: -t prints the time spent in the library call to stderr (the reference ignores unknown flags); binary PGM
-// (P5, maxval 255) is read and written directly (input recognised by its magic, output by "-f pgm" or a .pgm
-// name), for images beyond what stb_image can decode -- a PGM has no alpha, so like any image without alpha it is
-// all "inside" unless -l tests its grey values.
+// Added: -t prints the time spent in the library call to stderr (the reference ignores unknown flags); -g n cuts the
+// image into row bands over the first n GPUs of the box (chaqsdf_u8_multi; same bytes); binary PGM (P5, maxval 255)
+// is read and written directly (input recognised by its magic, output by "-f pgm" or a .pgm name), for images
+// beyond what stb_image can decode -- a PGM has no alpha, so like any image without alpha it is all "inside" unless
+// -l tests its grey values. A PGM with a lower maxval goes to stb_image like every other format (as in the reference);
+// a 16-bit PGM is refused: stb_image 2.27 -- the reference's decoder -- overruns its buffer converting it
+// (stb_image.h:1180 via :1743), so the reference itself crashes on such a file.
 //
 // Image decoding/encoding is stb_image / stb_image_write, compiled from the reference's include directory
 // (they are its third-party submodule; nothing is copied into this repository).
 #include <chrono>
+#include <climits>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -39,7 +43,7 @@ enum class Kind { Unknown, Png, Bmp, Jpg, Tga, Pgm };
 struct Options {
     const char* in = nullptr;
     const char* out = nullptr;
-    size_t spread = 64, quality = 100;
+    size_t spread = 64, quality = 100, gpus = 1;
     size_t channel = 1;  // 1 = alpha, 0 = luminance
     bool above = true, asymmetric = false, timing = false;
     bool from_stdin = false, to_stdout = false;
@@ -47,7 +51,7 @@ struct Options {
 };
 
 void print_usage() {
-    std::puts("usage: chaq_sdfgen [-f filetype] -i file -o file [-q n] [-s n] [-ahln]\n"
+    std::puts("usage: chaq_sdfgen [-f filetype] -i file -o file [-q n] [-s n] [-ahln] [-g n] [-t]\n"
               "    -f filetype   output type: png, bmp, jpg, tga (or pgm) (default: from the output name, else png)\n"
               "    -i file       input image; \"-\" reads stdin\n"
               "    -o file       output image; \"-\" writes stdout\n"
@@ -57,6 +61,7 @@ void print_usage() {
               "    -h            this text\n"
               "    -l            test the luminance instead of the alpha channel\n"
               "    -n            inverted test: values below the threshold are inside\n"
+              "    -g n          row bands over the first n GPUs of this box (default 1)\n"
               "    -t            print the time of the distance-field call to stderr");
 }
 
@@ -83,7 +88,7 @@ bool parse(int argc, char** argv, Options* o) {
         const char* a = argv[i];
         if (a[0] != '-') continue;
         const char key = a[1];
-        const bool takes_value = key == 'i' || key == 'o' || key == 's' || key == 'q' || key == 'f';
+        const bool takes_value = key == 'i' || key == 'o' || key == 's' || key == 'q' || key == 'f' || key == 'g';
         if (takes_value) {
             const char* val = (i + 1 < argc) ? argv[++i] : nullptr;
             switch (key) {
@@ -104,6 +109,11 @@ bool parse(int argc, char** argv, Options* o) {
                 case 'q':
                     if (!val) die(true, "No number specified with quality.");
                     o->quality = std::strtoull(val, nullptr, 10);
+                    break;
+                case 'g':
+                    if (!val) die(true, "No number specified with gpus.");
+                    o->gpus = std::strtoull(val, nullptr, 10);
+                    if (o->gpus == 0 || o->gpus > 64) die(true, "Invalid value given for gpus. Must be between 1-64");
                     break;
                 default:  // 'f'
                     if (!val) die(true, "Filetype not specified with filetype switch.");
@@ -130,23 +140,41 @@ bool parse(int argc, char** argv, Options* o) {
 
 void to_stdout(void*, void* data, int size) { std::fwrite(data, (size_t)size, 1, stdout); }
 
-// binary PGM: "P5" <w> <h> <maxval> <one whitespace> bytes; comments (#...) allowed between header tokens
-bool read_pgm_header(FILE* f, size_t* w, size_t* h) {
+// a byte source: a file, or a stream already in memory (stdin cannot be rewound)
+struct Src {
+    FILE* f = nullptr;
+    const unsigned char* p = nullptr;
+    size_t n = 0, i = 0;
+    int get() { return f ? std::fgetc(f) : (i < n ? p[i++] : EOF); }
+    size_t read(unsigned char* dst, size_t cnt) {
+        if (f) return std::fread(dst, 1, cnt, f);
+        const size_t k = cnt < n - i ? cnt : n - i;
+        std::memcpy(dst, p + i, k);
+        i += k;
+        return k;
+    }
+};
+
+// binary PGM: "P5" <w> <h> <maxval> <one whitespace> bytes; comments (#...) allowed between header tokens.
+// The source stands right after the magic. 0: not a header; 1: 8-bit (maxval 255); 2: a lower maxval (stb's job);
+// 3: 16-bit samples.
+int read_pgm_header(Src& in, size_t* w, size_t* h) {
     size_t v[3];
     for (int i = 0; i < 3; ++i) {
-        int c = std::fgetc(f);
+        int c = in.get();
         while (c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '#') {
-            if (c == '#') while (c != '\n' && c != EOF) c = std::fgetc(f);
-            c = std::fgetc(f);
+            if (c == '#') while (c != '\n' && c != EOF) c = in.get();
+            c = in.get();
         }
-        if (c < '0' || c > '9') return false;
+        if (c < '0' || c > '9') return 0;
         size_t x = 0;
-        while (c >= '0' && c <= '9') { x = x * 10 + (size_t)(c - '0'); c = std::fgetc(f); }
+        while (c >= '0' && c <= '9') { x = x * 10 + (size_t)(c - '0'); if (x > ((size_t)1 << 40)) return 0; c = in.get(); }
         v[i] = x;
-        if (i == 2 && !(c == ' ' || c == '\t' || c == '\n' || c == '\r')) return false;
+        if (i == 2 && !(c == ' ' || c == '\t' || c == '\n' || c == '\r')) return 0;
     }
     *w = v[0]; *h = v[1];
-    return v[2] == 255 && v[0] > 0 && v[1] > 0;
+    if (v[0] == 0 || v[1] == 0) return 0;
+    return v[2] == 255 ? 1 : (v[2] < 255 ? 2 : 3);
 }
 
 }  // namespace
@@ -158,43 +186,65 @@ int main(int argc, char** argv) {
     int w = 0, h = 0, n = 0;
     unsigned char* ya = nullptr;
     std::vector<unsigned char> grey;  // PGM input: one byte per pixel
-    FILE* fin = o.from_stdin ? stdin : std::fopen(o.in, "rb");
-    if (!fin) die(false, "Input file could not be opened.");
-    const int c0 = std::fgetc(fin), c1 = std::fgetc(fin);
-    if (c0 == 'P' && c1 == '5') {
-        size_t pw = 0, ph = 0;
-        if (!read_pgm_header(fin, &pw, &ph) || pw > 32768 || ph > 32768) die(false, "Input file could not be opened.");
-        grey.resize(pw * ph);
-        if (std::fread(grey.data(), 1, grey.size(), fin) != grey.size()) die(false, "Input file could not be opened.");
-        if (o.channel == 1) std::memset(grey.data(), 255, grey.size());  // no alpha channel: opaque everywhere
-        w = (int)pw; h = (int)ph;
+    std::vector<unsigned char> all;   // stdin: the whole stream
+    Src in;
+    if (o.from_stdin) {
+        unsigned char buf[1 << 16];
+        size_t got;
+        while ((got = std::fread(buf, 1, sizeof buf, stdin)) > 0) all.insert(all.end(), buf, buf + got);
+        in.p = all.data(); in.n = all.size();
     } else {
-        if (c1 != EOF) std::ungetc(c1, fin);
-        if (c0 != EOF) std::ungetc(c0, fin);  // two pushed-back bytes: fine for files; for pipes see below
+        in.f = std::fopen(o.in, "rb");
+        if (!in.f) die(false, "Input file could not be opened.");
+    }
+    bool is_pgm8 = false;
+    if (in.get() == 'P' && in.get() == '5') {
+        size_t pw = 0, ph = 0;
+        const int kind = read_pgm_header(in, &pw, &ph);
+        if (kind == 3) die(false, "16-bit PGM input is not supported (stb_image 2.27 overruns its buffer on it).");
+        if (kind == 1) {
+            if (pw > 32768 || ph > 32768)
+                die(false, "Input image is %zu x %zu: sides above 32768 are beyond this build's limit (CHAQSDF_MAX_DIM).", pw, ph);
+            grey.resize(pw * ph);
+            if (in.read(grey.data(), grey.size()) != grey.size()) die(false, "Input file could not be opened.");
+            if (o.channel == 1) std::memset(grey.data(), 255, grey.size());  // no alpha channel: opaque everywhere
+            w = (int)pw; h = (int)ph;
+            is_pgm8 = true;
+        }
+    }
+    if (in.f) std::fclose(in.f);
+    if (!is_pgm8) {  // every other format, including PGMs that are not 8-bit: stb_image, as the reference does
         if (o.from_stdin) {
-            // stdin may not take back two bytes: hand stb the whole stream from memory instead
-            std::vector<unsigned char> all;
-            unsigned char buf[1 << 16];
-            size_t got;
-            while ((got = std::fread(buf, 1, sizeof buf, fin)) > 0) all.insert(all.end(), buf, buf + got);
+            if (all.size() > (size_t)INT_MAX) die(false, "Input file could not be opened.");
             ya = stbi_load_from_memory(all.data(), (int)all.size(), &w, &h, &n, 2);
         } else {
-            std::fclose(fin);
-            fin = nullptr;
             ya = stbi_load(o.in, &w, &h, &n, 2);
         }
         if (!ya) die(false, "Input file could not be opened.");
+        if (w > 32768 || h > 32768)
+            die(false, "Input image is %d x %d: sides above 32768 are beyond this build's limit (CHAQSDF_MAX_DIM).", w, h);
     }
-    if (fin && fin != stdin) std::fclose(fin);
+    std::vector<unsigned char>().swap(all);
 
     std::vector<unsigned char> sdf((size_t)w * (size_t)h);
     const auto t0 = std::chrono::steady_clock::now();
-    const int rc = ya ? chaqsdf_u8(ya, (size_t)w, (size_t)h, 2, o.channel, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, sdf.data())
-                      : chaqsdf_u8(grey.data(), (size_t)w, (size_t)h, 1, 0, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, sdf.data());
+    const unsigned char* src = ya ? ya : grey.data();
+    const size_t stride = ya ? 2 : 1, chan = ya ? o.channel : 0;
+    int rc;
+    if (o.gpus > 1) {
+        std::vector<int> devs(o.gpus);
+        for (size_t k = 0; k < o.gpus; ++k) devs[k] = (int)k;
+        rc = chaqsdf_u8_multi(src, (size_t)w, (size_t)h, stride, chan, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, devs.data(),
+                              (int)devs.size(), sdf.data());
+    } else {
+        rc = chaqsdf_u8(src, (size_t)w, (size_t)h, stride, chan, o.above ? 1 : 0, o.spread, o.asymmetric ? 1 : 0, sdf.data());
+    }
     const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (ya) stbi_image_free(ya);
     if (rc != CHAQSDF_OK) die(false, "distance field failed (%d): %s", rc, chaqsdf_last_error_string());
-    if (o.timing) std::fprintf(stderr, "chaqsdf_u8: %dx%d spread %zu in %.3f ms (%.1f Mpix/s, host buffers)\n", w, h, o.spread, ms, w * (double)h / ms / 1e3);
+    if (o.timing)
+        std::fprintf(stderr, "chaqsdf_u8: %dx%d spread %zu on %zu GPU(s) in %.3f ms (%.1f Mpix/s, host buffers)\n", w, h, o.spread, o.gpus, ms,
+                     w * (double)h / ms / 1e3);
 
     if (!o.to_stdout && o.kind == Kind::Unknown) {
         if (const char* dot = std::strrchr(o.out, '.')) o.kind = kind_of(dot + 1);

@@ -179,6 +179,29 @@ int u8_pipelined(Pool& g_pool, const uint8_t* img, size_t w, size_t h, size_t st
     return CHAQSDF_OK;
 }
 
+// ---- several GPUs of one box, one process (chaqsdf_u8_multi) -------------------------------------------------
+// Pools of the multi-GPU entry are keyed by (device, position in the caller's device list), so that a device may
+// appear more than once (every position is a band with its own buffers; this is also how a one-GPU box tests it).
+std::map<std::pair<int, int>, Pool*> g_multi_pools;
+std::mutex g_multi_mu;  // one multi-GPU call at a time
+
+struct Shard {
+    int dev = 0;
+    size_t r0 = 0, r1 = 0, top = 0, bot = 0;  // image rows [r0, r1); halo rows held above / below them
+    Pool* pool = nullptr;
+    uint8_t *d_img = nullptr, *d_out = nullptr, *d_inter = nullptr;
+    void* d_ws = nullptr;
+    size_t ws_bytes = 0;
+    cudaEvent_t ev_p1 = nullptr;
+};
+
+int multi_fail(std::vector<Shard>& sh, int prev_dev, int code, const char* msg) {
+    for (auto& s : sh)
+        if (s.pool && s.pool->stream) { cudaSetDevice(s.dev); cudaStreamSynchronize(s.pool->stream); }
+    cudaSetDevice(prev_dev);
+    return msg ? set_error(code, msg) : code;
+}
+
 // {0,+INF} float heights -> 255/0 mask bytes; anything else raises the flag (general heights: not this path)
 __global__ void heights_to_mask_kernel(const float* __restrict__ f, uint8_t* __restrict__ m, size_t n, int* flag) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -238,6 +261,109 @@ int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t off
         return drained(g_pool, CHAQSDF_ERR_CUDA, "download failed");
     if (cudaStreamSynchronize(st) != cudaSuccess) return set_error(CHAQSDF_ERR_CUDA, "stream synchronisation failed");
     return CHAQSDF_OK;
+}
+
+// Row bands over several devices of this process (reference path: the same sdfgen.c:261-300, sharded). Pass 1 is per
+// row, so each device scans its own rows; pass 2 needs min(spread, distance to the image edge) rows of the
+// INTERMEDIATE from the bands above and below, which arrive by cudaMemcpyPeerAsync (NVLink when peer access exists,
+// staged by the driver otherwise) as soon as the owner's pass 1 has finished (cross-device event wait, no host
+// synchronisation). No torch, no NCCL: the exchange is a few MB between neighbours.
+int chaqsdf_u8_multi(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above, size_t spread,
+                     int asymmetric, const int* devices, int n_devices, uint8_t* out) {
+    if (!img || !out || !devices) return set_error(CHAQSDF_ERR_ARG, "null pointer");
+    if (n_devices < 1 || n_devices > 64) return set_error(CHAQSDF_ERR_ARG, "device count must be 1..64");
+    if (stride == 0 || offset >= stride) return set_error(CHAQSDF_ERR_ARG, "bad stride/offset");
+    if (w == 0 || h == 0) return set_error(CHAQSDF_ERR_ARG, "empty image");
+    if (w > CHAQSDF_MAX_DIM || h > CHAQSDF_MAX_DIM) return set_error(CHAQSDF_ERR_ARG, "image side exceeds 32768");
+    if (spread == 0) return set_error(CHAQSDF_ERR_ARG, "spread must be a positive integer");
+    int ndev = 0, prev_dev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || cudaGetDevice(&prev_dev) != cudaSuccess)
+        return set_error(CHAQSDF_ERR_CUDA, "no CUDA device");
+    for (int k = 0; k < n_devices; ++k)
+        if (devices[k] < 0 || devices[k] >= ndev) return set_error(CHAQSDF_ERR_ARG, "device index out of range");
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    const size_t rs = chaqsdf_inter_row_bytes(w, spread);
+    const size_t halo = spread < h ? spread : h;
+    std::vector<Shard> sh;
+    const size_t nb = (size_t)n_devices < h ? (size_t)n_devices : h;  // no empty bands
+    for (size_t k = 0; k < nb; ++k) {
+        Shard s;
+        s.dev = devices[k];
+        s.r0 = h * k / nb; s.r1 = h * (k + 1) / nb;
+        s.top = halo < s.r0 ? halo : s.r0;
+        s.bot = halo < h - s.r1 ? halo : h - s.r1;
+        sh.push_back(s);
+    }
+    // buffers, streams, events
+    for (size_t k = 0; k < nb; ++k) {
+        Shard& s = sh[k];
+        if (cudaSetDevice(s.dev) != cudaSuccess) return multi_fail(sh, prev_dev, CHAQSDF_ERR_CUDA, "cudaSetDevice failed");
+        Pool*& p = g_multi_pools[std::make_pair(s.dev, (int)k)];
+        if (!p) p = new Pool();
+        s.pool = p;
+        const size_t rows = s.r1 - s.r0, buf_rows = s.top + rows + s.bot;
+        s.ws_bytes = chaqsdf_envelope_workspace_bytes(w, buf_rows, spread);
+        void *a, *b, *c, *d;
+        if (pool_get(*p, 0, rows * w * stride, &a) != cudaSuccess || pool_get(*p, 1, rows * w, &b) != cudaSuccess ||
+            pool_get(*p, 2, buf_rows * rs, &c) != cudaSuccess || pool_get(*p, 3, s.ws_bytes ? s.ws_bytes : 256, &d) != cudaSuccess ||
+            pool_events(*p, 1) != cudaSuccess)
+            return multi_fail(sh, prev_dev, CHAQSDF_ERR_CUDA, "device allocation failed");
+        s.d_img = (uint8_t*)a; s.d_out = (uint8_t*)b; s.d_inter = (uint8_t*)c; s.d_ws = d;
+        s.ev_p1 = p->ev[0];
+        // direct NVLink copies between the bands' devices where the hardware allows (failure is fine: staged copies)
+        for (size_t q = 0; q < k; ++q)
+            if (sh[q].dev != s.dev) {
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, s.dev, sh[q].dev) == cudaSuccess && can) {
+                    cudaDeviceEnablePeerAccess(sh[q].dev, 0);
+                    cudaSetDevice(sh[q].dev);
+                    cudaDeviceEnablePeerAccess(s.dev, 0);
+                    cudaSetDevice(s.dev);
+                    cudaGetLastError();  // "already enabled" is not an error
+                }
+            }
+    }
+    // pass 1 on every band
+    for (Shard& s : sh) {
+        cudaSetDevice(s.dev);
+        cudaStream_t st = s.pool->stream;
+        const size_t rows = s.r1 - s.r0, row_bytes = w * stride;
+        if (cudaMemcpyAsync(s.d_img, img + s.r0 * row_bytes, rows * row_bytes, cudaMemcpyHostToDevice, st) != cudaSuccess)
+            return multi_fail(sh, prev_dev, CHAQSDF_ERR_CUDA, "upload failed");
+        int rc = chaqsdf_rowscan_device(s.d_img, w, rows, stride, offset, test_above, spread, s.d_inter + s.top * rs, st);
+        if (rc) return multi_fail(sh, prev_dev, rc, nullptr);
+        if (cudaEventRecord(s.ev_p1, st) != cudaSuccess) return multi_fail(sh, prev_dev, CHAQSDF_ERR_CUDA, "event record failed");
+    }
+    // halo rows from the owners, pass 2, download
+    for (size_t k = 0; k < nb; ++k) {
+        Shard& s = sh[k];
+        cudaSetDevice(s.dev);
+        cudaStream_t st = s.pool->stream;
+        const size_t lo = s.r0 - s.top, hi = s.r1 + s.bot;  // image rows this band's buffer holds
+        for (size_t q = 0; q < nb; ++q) {
+            if (q == k) continue;
+            const Shard& o = sh[q];
+            const size_t a = o.r0 > lo ? o.r0 : lo, b = o.r1 < hi ? o.r1 : hi;  // rows owned by q that k needs
+            if (a >= b) continue;
+            if (cudaStreamWaitEvent(st, o.ev_p1, 0) != cudaSuccess ||
+                cudaMemcpyPeerAsync(s.d_inter + (a - lo) * rs, s.dev, o.d_inter + (o.top + a - o.r0) * rs, o.dev, (b - a) * rs,
+                                    st) != cudaSuccess)
+                return multi_fail(sh, prev_dev, CHAQSDF_ERR_CUDA, "halo copy failed");
+        }
+        const size_t rows = s.r1 - s.r0;
+        int rc = chaqsdf_envelope_device(s.d_inter, w, s.top + rows + s.bot, s.top, s.top + rows, spread, asymmetric, s.d_out,
+                                         s.d_ws, s.ws_bytes, st);
+        if (rc) return multi_fail(sh, prev_dev, rc, nullptr);
+        if (cudaMemcpyAsync(out + s.r0 * w, s.d_out, rows * w, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+            return multi_fail(sh, prev_dev, CHAQSDF_ERR_CUDA, "download failed");
+    }
+    int rc = CHAQSDF_OK;
+    for (Shard& s : sh) {
+        cudaSetDevice(s.dev);
+        if (cudaStreamSynchronize(s.pool->stream) != cudaSuccess) rc = set_error(CHAQSDF_ERR_CUDA, "multi-GPU pipeline failed");
+    }
+    cudaSetDevice(prev_dev);
+    return rc;
 }
 
 // General heights (or CHAQSDF_DT2D=stock): the reference's float32 envelope, one thread per line (dt_float.cuh).

@@ -28,7 +28,7 @@ def build_library(force=False):
 SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count", "chaqsdf_reload_tuning",
            "chaqsdf_profile_enable",
            "chaqsdf_profile_mean_ms", "dist_transform_2d",
-           "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_pipeline_plan", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
+           "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_u8_multi", "chaqsdf_pipeline_plan", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
            "chaqsdf_inter_row_bytes",
            "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
@@ -53,6 +53,7 @@ def lib():
     L.dist_transform_2d.argtypes = [vp, sz, sz]
     L.dist_transform_2d.restype = None
     L.chaqsdf_u8.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp]
+    L.chaqsdf_u8_multi.argtypes = [vp, sz, sz, sz, sz, i, sz, i, C.POINTER(C.c_int), i, vp]
     L.chaqsdf_pipeline_plan.argtypes = [sz, sz, sz, sz, C.POINTER(sz), sz]
     L.chaqsdf_pipeline_plan.restype = sz
     L.chaqsdf_workspace_bytes.argtypes = [sz, sz, sz]
@@ -137,6 +138,18 @@ def sdf_u8(img, w, h, stride=1, offset=0, test_above=True, spread=64, asymmetric
 
 
 # ---------------------------------------------------------------- device entry points (torch tensors)
+def sdf_u8_multi(img, w, h, devices, stride=1, offset=0, test_above=True, spread=64, asymmetric=False, out=None):
+    """Host buffers in and out, row bands over the listed devices of this process (chaqsdf_u8_multi)."""
+    import numpy as np
+    src = np.ascontiguousarray(img, np.uint8)
+    if out is None:
+        out = np.empty((h, w), np.uint8)
+    devs = (C.c_int * len(devices))(*devices)
+    _check(lib().chaqsdf_u8_multi(src.ctypes.data_as(C.c_void_p), w, h, stride, offset, int(test_above), spread,
+                                  int(asymmetric), devs, len(devices), out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
 def pipeline_plan(w, h, stride=1, spread=64):
     """Band heights (rows, top to bottom) chaqsdf_u8 uses for a host image of this shape; [] = one shot."""
     buf = (C.c_size_t * 4096)()

@@ -78,6 +78,14 @@ int chaqsdf_u8(const uint8_t* img, size_t w, size_t h, size_t stride, size_t off
  * their heights in rows, top to bottom. Host-only (no device needed); honours CHAQSDF_PIPE_ROWS / _FIRST. */
 size_t chaqsdf_pipeline_plan(size_t w, size_t h, size_t stride, size_t spread, size_t* bands, size_t max_bands);
 
+/* The same over several GPUs of one box, from one process and one host thread: the image is cut
+ * into n_devices row bands, band k on devices[k] (a device may be listed more than once). Each device uploads and
+ * scans its own rows; the spread rows of the intermediate that pass 2 needs from the neighbouring bands move device
+ * to device (cudaMemcpyPeerAsync; NVLink where peer access exists) behind cross-device event waits; the bands' bytes
+ * are downloaded into out. Byte-identical to chaqsdf_u8. The caller's current device is restored. */
+int chaqsdf_u8_multi(const uint8_t* img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
+                     size_t spread, int asymmetric, const int* devices, int n_devices, uint8_t* out);
+
 /* ---- device-resident path -------------------------------------------------------------------------
  * d_img/d_out/d_workspace are device pointers on the current device; stream is a cudaStream_t (NULL =
  * default stream). No allocation or synchronisation inside once the per-(device,spread,asymmetric)

@@ -567,3 +567,72 @@ def test_narrow_rows_several_per_warp(pkg, oracle):
     got = out.cpu().numpy()
     for k in range(n):
         assert np.array_equal(got[k], oracle.sdf(imgs[k], s, s, spread=16)), k
+
+
+def test_multi_device_entry(pkg, oracle):
+    """chaqsdf_u8_multi: row bands over a list of devices of this process (host buffers in and out), byte-identical to
+    the oracle. A device may be listed more than once -- every position is a band with its own buffers -- so one GPU
+    checks the band logic too: halos from one neighbour, from several (spread larger than a band), the general
+    intermediate (spread > 256), strided input, more devices than rows."""
+    rng = np.random.default_rng(53)
+    ngpu = torch.cuda.device_count()
+    lists = [[0], [0, 0], [0, 0, 0, 0, 0]] + ([list(range(ngpu)), list(range(ngpu)) * 2] if ngpu > 1 else [])
+    w, h = 640, 900
+    img = oracle.syn_discs(w, h)
+    for devs in lists:
+        for spread, asym in ((40, False), (256, True), (300, False), (1000, False)):
+            got = pkg.sdf_u8_multi(img, w, h, devs, spread=spread, asymmetric=asym)
+            assert np.array_equal(got, oracle.sdf(img, w, h, spread=spread, asymmetric=asym)), (devs, spread)
+    ya = rng.integers(0, 256, (333, 500, 2), dtype=np.uint8)
+    ya[100:200, 50:400] = (3, 250)
+    got = pkg.sdf_u8_multi(ya, 500, 333, [0, 0, 0], stride=2, offset=1, test_above=False, spread=20)
+    assert np.array_equal(got, oracle.sdf(ya, 500, 333, stride=2, offset=1, test_above=False, spread=20))
+    tiny = random_shapes(rng, 3, 70)
+    assert np.array_equal(pkg.sdf_u8_multi(tiny, 70, 3, [0] * 8, spread=5), oracle.sdf(tiny, 70, 3, spread=5))
+    big = oracle.syn_discs(4096)  # large enough for every band to be a real launch
+    want = oracle.sdf(big, 4096, 4096, spread=64)
+    for devs in lists[1:]:
+        assert np.array_equal(pkg.sdf_u8_multi(big, 4096, 4096, devs, spread=64), want), devs
+    with pytest.raises(pkg.ChaqSdfError):
+        pkg.sdf_u8_multi(img, w, h, [ngpu], spread=8)  # no such device
+    assert torch.cuda.current_device() == 0
+
+
+def test_cli_gpus_flag_and_16bit_pgm(pkg, oracle, tmp_path):
+    """-g n (row bands over the first n GPUs, chaqsdf_u8_multi) gives the same file as the single-GPU run; a 16-bit PGM
+    is not for the private 8-bit reader and goes to stb_image like every other format (as the reference would)."""
+    import subprocess
+    cli = os.path.join(ROOT, "chaq-sdfgen_b200", "bin", "chaq_sdfgen")
+    if not os.path.exists(cli):
+        pytest.skip("bin/chaq_sdfgen not built")
+    n = 700
+    img = oracle.syn_discs(n)
+    src, a, b = tmp_path / "in.pgm", tmp_path / "a.pgm", tmp_path / "b.pgm"
+    src.write_bytes(b"P5\n%d %d\n255\n" % (n, n) + img.tobytes())
+    g = min(torch.cuda.device_count(), 4)
+    r = subprocess.run([cli, "-i", str(src), "-o", str(a), "-s", "30", "-l"], capture_output=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([cli, "-i", str(src), "-o", str(b), "-s", "30", "-l", "-g", str(g), "-t"], capture_output=True, timeout=120)
+    assert r.returncode == 0 and b"GPU(s)" in r.stderr, r.stderr
+    assert a.read_bytes() == b.read_bytes()
+    assert np.array_equal(np.frombuffer(a.read_bytes()[-n * n:], np.uint8).reshape(n, n), oracle.sdf(img, n, n, spread=30))
+    r = subprocess.run([cli, "-i", str(src), "-o", str(b), "-g", str(torch.cuda.device_count() + 1)], capture_output=True, timeout=120)
+    assert r.returncode == 255 and b"device index out of range" in r.stderr
+    r = subprocess.run([cli, "-i", str(src), "-o", str(b), "-g", "0"], capture_output=True, timeout=120)
+    assert r.returncode == 255 and b"Invalid value given for gpus" in r.stderr
+    # a PGM with a lower maxval is stb_image's (raw bytes, as in the reference); a 16-bit one is refused with a message
+    small = np.ascontiguousarray(img[:90, :120]) // 2  # values 0 / 127: with -l (> 127) nothing is inside
+    small[10:40, 20:70] = 200
+    low = tmp_path / "low.pgm"
+    low.write_bytes(b"P5\n120 90\n200\n" + small.tobytes())
+    r = subprocess.run([cli, "-i", str(low), "-o", str(a), "-s", "9", "-l", "-f", "pgm"], capture_output=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    got = np.frombuffer(a.read_bytes()[-90 * 120:], np.uint8).reshape(90, 120)
+    assert np.array_equal(got, oracle.sdf(small, 120, 90, spread=9))
+    r = subprocess.run([cli, "-i", "-", "-o", "-", "-s", "9", "-l", "-f", "pgm"], input=low.read_bytes(), capture_output=True, timeout=120)
+    assert r.returncode == 0 and np.array_equal(np.frombuffer(r.stdout[-90 * 120:], np.uint8).reshape(90, 120), got)
+    wide = (small.astype(np.uint16) * 257).astype(">u2")
+    src16 = tmp_path / "in16.pgm"
+    src16.write_bytes(b"P5\n120 90\n65535\n" + wide.tobytes())
+    r = subprocess.run([cli, "-i", str(src16), "-o", str(a), "-s", "9", "-l"], capture_output=True, timeout=120)
+    assert r.returncode == 255 and b"16-bit PGM" in r.stderr
