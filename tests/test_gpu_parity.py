@@ -636,3 +636,32 @@ def test_cli_gpus_flag_and_16bit_pgm(pkg, oracle, tmp_path):
     src16.write_bytes(b"P5\n120 90\n65535\n" + wide.tobytes())
     r = subprocess.run([cli, "-i", str(src16), "-o", str(a), "-s", "9", "-l"], capture_output=True, timeout=120)
     assert r.returncode == 255 and b"16-bit PGM" in r.stderr
+
+
+def test_reference_main_runs_on_the_dropin(pkg, tmp_path):
+    """The reference's own main (openmp/sdfgen.c, unmodified) linked against libchaqsdf_b200.so instead of df.c
+    (oracle/Makefile builds oracle/_ref/chaq_sdfgen_dropin where the reference tree exists):
+    the README example through it must give the reference's sample output. Its two OpenMP section threads call
+    dist_transform_2d at the same time (sdfgen.c:277-289)."""
+    import subprocess
+    from PIL import Image
+    exe = os.path.join(ROOT, "oracle", "_ref", "chaq_sdfgen_dropin")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/chaq_sdfgen_dropin not built (needs the reference tree)")
+    z = np.load(os.path.join(GOLDEN, "sample_pair.npz"))
+    ya = z["ya"].reshape(200, 200, 2)
+    src, dst = tmp_path / "in.png", tmp_path / "out.png"
+    Image.fromarray(np.ascontiguousarray(ya[:, :, 0]), "L").save(src)
+    for _ in range(3):
+        r = subprocess.run([exe, "-i", str(src), "-o", str(dst), "-s", "100", "-al"], capture_output=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        assert np.array_equal(np.asarray(Image.open(dst)), z["out"])
+    big = tmp_path / "big.png"  # larger, non-trivial alpha test (default flags), both section threads busy for a while
+    rng = np.random.default_rng(5)
+    rgba = np.zeros((1500, 1500, 4), np.uint8)
+    rgba[..., 3] = random_shapes(rng, 1500, 1500)
+    Image.fromarray(rgba, "RGBA").save(big)
+    r = subprocess.run([exe, "-i", str(big), "-o", str(dst), "-s", "32"], capture_output=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    from oracle import Oracle
+    assert np.array_equal(np.asarray(Image.open(dst)), Oracle().sdf(np.ascontiguousarray(rgba[..., 3]), 1500, 1500, spread=32))

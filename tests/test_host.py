@@ -232,6 +232,24 @@ def test_host_pipeline_band_schedule(pkg, monkeypatch):
     pkg.reload_tuning()
 
 
+def test_reference_main_links_against_the_dropin(pkg, tmp_path):
+    """INTEGRATION.md section 1 as a build: the reference's own program (openmp/sdfgen.c, unmodified, where it lies in
+    the reference tree) compiled WITHOUT openmp/df.c and linked against libchaqsdf_b200.so; dist_transform_2d must be
+    the only thing it takes from the library. (Running it is a GPU test: test_reference_main_runs_on_the_dropin.)"""
+    ref_c = "/root/reference/openmp/sdfgen.c"
+    if not os.path.exists(ref_c):
+        pytest.skip("reference tree absent")
+    exe = tmp_path / "chaq_sdfgen"
+    libdir = os.path.join(ROOT, "chaq-sdfgen_b200")
+    r = subprocess.run(["/usr/bin/gcc", "-std=c11", "-O3", "-fopenmp", "-w", "-I/root/reference/include", ref_c, "-L" + libdir,
+                        "-lchaqsdf_b200", "-Wl,-rpath," + libdir, "-lm", "-o", str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    und = subprocess.run(["nm", "-D", "--undefined-only", str(exe)], capture_output=True, text=True).stdout
+    assert "dist_transform_2d" in und and "chaqsdf_" not in und
+    r = subprocess.run([str(exe), "-h"], capture_output=True, text=True, timeout=60)  # the reference's own usage text
+    assert r.returncode == 0 and r.stdout.startswith("usage: chaq_sdfgen")
+
+
 def test_syn_glyph_generators_agree(oracle):
     """SYN-GLYPH exists twice (C in the oracle for the tests, numpy in bench.py for the GPU box): same bytes."""
     import bench
