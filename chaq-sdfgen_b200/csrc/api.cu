@@ -143,11 +143,15 @@ int cap_for(size_t spread) { return spread + 1 > 0x7fff ? 0x7fff : (int)(spread 
 // ---- intermediate formats --------------------------------------------------------------------------------
 // banded (spread <= 256): per row [Wp bytes g8 | Wp/8 bytes class bits | one busy byte per 128-column strip,
 //                        padded to 16], Wp = w rounded up to 128
+// banded, 257..1024    : per row [2*Wp bytes g16 | Wp/8 bytes class bits]
 // general               : per row w uint16 (bit 15 class, bits 0..14 row distance saturated at spread+1)
-bool banded(size_t spread) { return spread <= 256; }
+// banded path: hull build / merge / paint over records. Row distances are bytes up to spread 256, uint16 up to 1024.
+bool banded(size_t spread) { return spread <= 1024; }
+bool banded_wide(size_t spread) { return spread > 256 && spread <= 1024; }
 int banded_wp(size_t w) { return (int)align_up(w, 128); }
-size_t banded_rs(size_t w) {
+size_t banded_rs(size_t w, size_t spread) {
     const size_t wp = (size_t)banded_wp(w);
+    if (banded_wide(spread)) return 2 * wp + wp / 8;
     return wp + wp / 8 + align_up(wp / 128, 16);
 }
 // scratch of the banded pass 2 (hull.cuh, paint.cuh): hull bitmask + transposed class bits (one word per
@@ -160,7 +164,7 @@ size_t hull_ws_bytes(size_t n_img, size_t w, size_t buf_rows) {
     const size_t nblk = (buf_rows + 31) / 32, ncg = (w + 31) / 32;
     return 2 * hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256);
 }
-size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w) : w * sizeof(uint16_t); }
+size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w, spread) : w * sizeof(uint16_t); }
 
 // launch geometry of the general pass 2
 struct EnvPlan {
@@ -227,7 +231,7 @@ int launch_env(const EnvPlan& pl, const EnvParams& p, bool fields, cudaStream_t 
 
 int launch_rowscan(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above, int cap,
                    uint16_t* d_inter, cudaStream_t st) {
-    RowScanParams rp;
+    RowScanParams rp{};
     rp.img = d_img; rp.inter = d_inter; rp.rows = (long long)rows; rp.w = (int)w;
     rp.stride = (int)stride; rp.offset = (int)offset; rp.above = test_above ? 1 : 0; rp.cap = cap;
     rp.nwords = (int)((w + 31) / 32);
@@ -238,11 +242,26 @@ int launch_rowscan(const uint8_t* d_img, size_t w, size_t rows, size_t stride, s
     return CHAQSDF_OK;
 }
 
+// pass 1 of the banded path for spreads 257..1024: the general scan, writing records with 16-bit row distances
+int launch_rowscan_rec(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
+                       size_t spread, uint8_t* d_inter, cudaStream_t st) {
+    RowScanParams rp{};
+    rp.img = d_img; rp.inter = (uint16_t*)d_inter; rp.rows = (long long)rows; rp.w = (int)w;
+    rp.stride = (int)stride; rp.offset = (int)offset; rp.above = test_above ? 1 : 0; rp.cap = (int)spread + 1;
+    rp.nwords = (int)((w + 31) / 32);
+    rp.record = 1; rp.wp = banded_wp(w); rp.rs_bytes = (long long)banded_rs(w, spread);
+    const size_t smem = (size_t)kRowWarps * rp.nwords * sizeof(uint32_t);
+    const unsigned blocks = (unsigned)((rows + kRowWarps - 1) / kRowWarps);
+    rowscan_kernel<<<blocks, kRowWarps * 32, smem, st>>>(rp);
+    CQ_LAUNCHED("rowscan_kernel<records>", blocks, smem);
+    return CHAQSDF_OK;
+}
+
 // ---- banded path -------------------------------------------------------------------------------------------
 int launch_rowscan8(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
                     size_t spread, uint8_t* d_inter, cudaStream_t st) {
     RowScan8Params rp;
-    rp.img = d_img; rp.inter = d_inter; rp.rows = (long long)rows; rp.rs = (long long)banded_rs(w);
+    rp.img = d_img; rp.inter = d_inter; rp.rows = (long long)rows; rp.rs = (long long)banded_rs(w, spread);
     rp.wp = banded_wp(w); rp.w = (int)w; rp.stride = (int)stride; rp.offset = (int)offset;
     rp.above = test_above ? 1 : 0; rp.cap = spread + 1 > 256 ? 256 : (int)(spread + 1);
     rp.nwords = (int)((w + 31) / 32);
@@ -315,8 +334,9 @@ void prof_mark(int i, cudaStream_t st) {
     if (i == 3) ++g_prof_n;
 }
 
-// banded pass 2 as build / merge / emit (hull.cuh)
-int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
+// banded pass 2 as build / merge / paint (hull.cuh, paint.cuh)
+template <bool WIDE>
+int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
                 const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st) {
     DevInfo di;
     if (int rc = device_info(&di)) return rc;
@@ -326,7 +346,8 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     p.hull = (uint32_t*)d_ws;
     p.clsT = (uint32_t*)((uint8_t*)d_ws + hull_words_bytes(n_img, w, buf_rows));
     p.flags = (uint8_t*)d_ws + 2 * hull_words_bytes(n_img, w, buf_rows);
-    p.rs = (long long)banded_rs(w); p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
+    p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
+    p.rs = (long long)banded_rs(w, WIDE ? 1024 : 256); p.cls_off = WIDE ? 2 * p.wp : p.wp;
     p.nblk = (int)((buf_rows + 31) / 32);
     p.ncg = (int)((w + 31) / 32); p.wc = p.ncg * 32;
     p.nstrips = (p.ncg + kHullWarps - 1) / kHullWarps; p.n_img = (int)n_img;
@@ -343,7 +364,7 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     if (pb < pb_par) pb = pb_par;
     if (g_tuning.hull_pb > 0) pb = g_tuning.hull_pb;
     if (pb < 1) pb = 1;
-    if (pb > kHullMaxPieceBlocks) pb = kHullMaxPieceBlocks;
+    if (pb > hull_max_run_blocks(WIDE)) pb = hull_max_run_blocks(WIDE);
     if (pb > p.nblk) pb = p.nblk;
     p.pb = (int)pb; p.nruns_b = (p.nblk + p.pb - 1) / p.pb;
     // Few build CTAs (a band of a pipelined or sharded image): what matters is the chain of pushes down one run, so
@@ -362,10 +383,14 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
     p.eb = (int)eb; p.nruns_e = (nbo + p.eb - 1) / p.eb;
     const long long gb = strips * p.nruns_b, ge = (long long)n_img * p.nstrips_e * p.nruns_e;
     if (gb > 0x7fffffffLL || ge > 0x7fffffffLL) return fail(CHAQSDF_ERR_ARG, "too many runs for one grid");
-    const size_t smem_b = hull_build_smem(p.pb, p.nsub), smem_e = hull_paint_smem();
+    const size_t smem_b = hull_build_smem(p.pb, p.nsub, WIDE), smem_e = hull_paint_smem();
+    if (smem_b > 48 * 1024) {
+        CQ_CUDA(cudaFuncSetAttribute(hull_build_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+        CQ_CUDA(cudaFuncSetAttribute(hull_build4_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+    }
     prof_mark(0, st);
-    if (p.nsub == 4) hull_build4_kernel<<<(unsigned)gb, kHullWarps * 32 * 4, smem_b, st>>>(p);
-    else hull_build_kernel<<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
+    if (p.nsub == 4) hull_build4_kernel<WIDE><<<(unsigned)gb, kHullWarps * 32 * 4, smem_b, st>>>(p);
+    else hull_build_kernel<WIDE><<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
     CQ_LAUNCHED(p.nsub == 4 ? "hull_build4_kernel" : "hull_build_kernel", gb, smem_b);
     prof_mark(1, st);
     if (p.nruns_b > 1 && !g_tuning.hull_seq) {
@@ -379,20 +404,32 @@ int launch_hull(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_be
             p.merge_phase = phase;
             const long long thr = (long long)n_img * nmine * p.w;
             const unsigned gm = (unsigned)((thr + 255) / 256);
-            hull_merge_par_kernel<<<gm, 256, 0, st>>>(p);
+            hull_merge_par_kernel<WIDE><<<gm, 256, 0, st>>>(p);
             CQ_LAUNCHED("hull_merge_par_kernel", gm, 0);
         }
     } else if (p.nruns_b > 1) {
         const long long cols = (long long)n_img * p.w;
         const unsigned gm = (unsigned)((cols + 255) / 256);
-        hull_merge_kernel<<<gm, 256, 0, st>>>(p);
+        hull_merge_kernel<WIDE><<<gm, 256, 0, st>>>(p);
         CQ_LAUNCHED("hull_merge_kernel", gm, 0);
     }
     prof_mark(2, st);
-    hull_paint_kernel<<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
+    hull_paint_kernel<WIDE><<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
     CQ_LAUNCHED("hull_paint_kernel", ge, smem_e);
     prof_mark(3, st);
     return CHAQSDF_OK;
+}
+
+int launch_hull(size_t spread, const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
+                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st) {
+    if (tab->hl.cap_eff > (banded_wide(spread) ? 1025 : 256)) return fail(CHAQSDF_ERR_ARG, "internal: banded path beyond its reach");
+    if (banded_wide(spread)) return launch_hull_t<true>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st);
+    return launch_hull_t<false>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st);
+}
+int launch_pass1_banded(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
+                        size_t spread, uint8_t* d_inter, cudaStream_t st) {
+    if (banded_wide(spread)) return launch_rowscan_rec(d_img, w, rows, stride, offset, test_above, spread, d_inter, st);
+    return launch_rowscan8(d_img, w, rows, stride, offset, test_above, spread, d_inter, st);
 }
 
 }  // namespace
@@ -440,7 +477,7 @@ size_t chaqsdf_inter_row_bytes(size_t w, size_t spread) {
 
 size_t chaqsdf_batched_workspace_bytes(size_t n, size_t w, size_t h, size_t spread) {
     if (check_dims(w, h, spread) || n == 0) return 0;
-    if (banded(spread)) return align_up(n * h * banded_rs(w), 256) + hull_ws_bytes(n, w, h);
+    if (banded(spread)) return align_up(n * h * banded_rs(w, spread), 256) + hull_ws_bytes(n, w, h);
     EnvPlan pl;
     if (plan_envelope(w, h, h, n, cap_for(spread), &pl)) return 0;
     return align_up(n * w * h * sizeof(uint16_t), 256) + pl.ring_bytes;
@@ -470,7 +507,7 @@ int chaqsdf_rowscan_device(const uint8_t* d_img, size_t w, size_t rows, size_t s
     if (spread == 0) return fail(CHAQSDF_ERR_ARG, "spread must be a positive integer");
     if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
     if (banded(spread))
-        return launch_rowscan8(d_img, w, rows, stride, offset, test_above, spread, (uint8_t*)d_inter, (cudaStream_t)stream);
+        return launch_pass1_banded(d_img, w, rows, stride, offset, test_above, spread, (uint8_t*)d_inter, (cudaStream_t)stream);
     return launch_rowscan(d_img, w, rows, stride, offset, test_above, cap_for(spread), (uint16_t*)d_inter,
                           (cudaStream_t)stream);
 }
@@ -484,8 +521,7 @@ int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size
     const Tables* tab;
     if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     if (banded(spread)) {
-        if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
-        return launch_hull((const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
+        return launch_hull(spread, (const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
                            workspace_bytes, (cudaStream_t)stream);
     }
     EnvPlan pl;
@@ -510,16 +546,15 @@ int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t 
     if (int rc = get_table(spread, asymmetric, &tab)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     if (banded(spread)) {
-        if (tab->hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path with cap_eff > 256");
         DevInfo di;
         if (int rc = device_info(&di)) return rc;
         // batches of small images with a small spread: one CTA per image, nothing but the bytes in and out touches HBM
         if (n <= 0x7fffffff && (n >= 2 || g_tuning.glyph == 2) && glyph_fits(w, h, stride, tab, di))
             return launch_glyph(d_imgs, n, w, h, test_above, tab, d_out, st);
-        const size_t inter_bytes = align_up(n * h * banded_rs(w), 256);
+        const size_t inter_bytes = align_up(n * h * banded_rs(w, spread), 256);
         if (workspace_bytes < inter_bytes + hull_ws_bytes(n, w, h)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
-        if (int rc = launch_rowscan8(d_imgs, w, n * h, stride, offset, test_above, spread, (uint8_t*)d_workspace, st)) return rc;
-        return launch_hull((const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
+        if (int rc = launch_pass1_banded(d_imgs, w, n * h, stride, offset, test_above, spread, (uint8_t*)d_workspace, st)) return rc;
+        return launch_hull(spread, (const uint8_t*)d_workspace, w, h, 0, h, n, tab, d_out, (char*)d_workspace + inter_bytes,
                            workspace_bytes - inter_bytes, st);
     }
     const int cap = cap_for(spread);

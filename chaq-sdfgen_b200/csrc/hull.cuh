@@ -24,6 +24,14 @@
 namespace chaq {
 
 constexpr int kHullWarps = 4;
+
+// Row distances in pass 1's record: one byte (spread <= 256) or, WIDE, one uint16 (spread <= 1024). Same kernels.
+template <bool WIDE> struct GVal { typedef uint8_t T; };
+template <> struct GVal<true> { typedef uint16_t T; };
+template <bool WIDE>
+__device__ __forceinline__ uint32_t g_load(const uint8_t* p) {
+    return (uint32_t)__ldg(reinterpret_cast<const typename GVal<WIDE>::T*>(p));
+}
 #ifndef CQ_EMIT_WARPS
 #define CQ_EMIT_WARPS 4
 #endif
@@ -36,7 +44,8 @@ struct HullParams {
     uint32_t* hull;          // [n_img][nblk][wc] hull words
     uint8_t* flags;          // [n_img][nblk][ncg] block flags
     uint32_t* clsT;          // [n_img][nblk][wc] class bits, transposed like the hull words (bit j = row 32*blk+j)
-    long long rs;            // record stride
+    long long rs;            // record stride, bytes
+    int cls_off;             // byte offset of the class bit-plane inside a record (after the row distances)
     int wp, w, buf_rows, nblk;
     int wc;                  // ncg * 32
     int ncg, nstrips, n_img;
@@ -51,16 +60,19 @@ struct HullParams {
     int merge_phase, merge_nphase;  // parallel merge: this launch repairs junctions k = 1 + phase + i*nphase
 };
 
-__host__ __device__ inline size_t hull_build_smem(int pb, int nsub) {
-    return (size_t)kHullWarps * ((size_t)nsub * 2 * 1024 + (size_t)pb * 128);
+__host__ __device__ inline size_t hull_build_smem(int pb, int nsub, bool wide) {
+    return (size_t)kHullWarps * ((size_t)nsub * 2 * (wide ? 2048 : 1024) + (size_t)pb * 128);
 }
 
+template <bool WIDE>
 struct HullBuildCtx {
-    const uint8_t* gst;      // staging (2 blocks of 32 rows x 32 bytes), generic pointer at lane 0
+    typedef typename GVal<WIDE>::T G;
+    static constexpr int kSlot = 1024 * (int)sizeof(G);  // one staged block: 32 rows x 32 columns
+    const uint8_t* gst;      // staging (2 blocks), generic pointer at lane 0
     uint32_t gst_s;          // the same, shared-space address
     uint32_t* bits;          // run's hull words, already offset by lane
     const uint8_t* rec0;     // record of buffer row 0 at this warp's first column
-    const uint8_t* rec_lane; // rec0 + lane
+    const uint8_t* rec_lane; // the same at this lane's column
     const uint8_t* cls0;     // class word of buffer row 0 for this column group
     uint8_t* flag0;          // flags of block 0 for this column group (stride ncg per block)
     uint32_t* clst0;         // transposed class word of block 0 for this lane's column (stride wc per block)
@@ -73,11 +85,12 @@ struct HullBuildCtx {
 
     __device__ __forceinline__ void issue(int blk, int s) {
         if (blk < blk_end) {
+            constexpr int kPieces = 2 * (int)sizeof(G);  // 16-byte pieces per row of 32 columns
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const int q = lane + 32 * i, row = q >> 1, half = q & 1;
+            for (int i = 0; i < kPieces; ++i) {
+                const int q = lane + 32 * i, row = q / kPieces, piece = q % kPieces;
                 const int r = blk * 32 + row;
-                if (r < nrows) cp_async16(gst_s + s * 1024 + row * 32 + half * 16, rec0 + (long long)r * rs + half * 16);
+                if (r < nrows) cp_async16(gst_s + s * kSlot + row * (32 * (int)sizeof(G)) + piece * 16, rec0 + (long long)r * rs + piece * 16);
             }
         }
         cp_async_commit();
@@ -95,20 +108,30 @@ struct HullBuildCtx {
         cur_blk = blk;
     }
     __device__ __forceinline__ bool block_quiet(int L) const {
-        const uint32_t* wds = reinterpret_cast<const uint32_t*>(gst + slot * 1024);
-        const uint32_t lim = (uint32_t)L * 0x01010101u;
+        const uint32_t* wds = reinterpret_cast<const uint32_t*>(gst + slot * kSlot);
         const int rows_here = nrows - cur_blk * 32;
         uint32_t m = 0xFFFFFFFFu;
+        if (WIDE) {
+            const uint32_t lim = (uint32_t)L * 0x00010001u;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < 16; ++i) {  // 16 words per row
+                const uint32_t v = wds[lane + 32 * i];
+                const bool live = (lane >> 4) + 2 * i < rows_here;
+                m = __vminu2(m, live ? v : 0xFFFFFFFFu);
+            }
+            return __all_sync(0xffffffffu, __vcmpgeu2(m, lim) == 0xFFFFFFFFu);
+        }
+        const uint32_t lim = (uint32_t)L * 0x01010101u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {  // 8 words per row
             const uint32_t v = wds[lane + 32 * i];
             const bool live = (lane >> 3) + 4 * i < rows_here;
             m = __vminu4(m, live ? v : 0xFFFFFFFFu);
         }
         return __all_sync(0xffffffffu, __vcmpgeu4(m, lim) == 0xFFFFFFFFu);
     }
-    __device__ __forceinline__ uint32_t g_push(int j) const { return gst[slot * 1024 + j * 32 + lane]; }
-    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_lane + (unsigned)r * rs32); }
+    __device__ __forceinline__ uint32_t g_push(int j) const { return reinterpret_cast<const G*>(gst + slot * kSlot)[j * 32 + lane]; }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return g_load<WIDE>(rec_lane + (unsigned)r * rs32); }
     __device__ __forceinline__ uint32_t bits_ld(int i) const { return bits[i * 32]; }
     __device__ __forceinline__ void bits_st(int i, uint32_t v) { bits[i * 32] = v; }
     __device__ __forceinline__ void block_end(int blk, uint32_t word) {
@@ -120,6 +143,7 @@ struct HullBuildCtx {
 };
 
 // junction repair inside a build CTA: the run's hull words are still in shared memory
+template <bool WIDE>
 struct HullRunMergeCtx {
     uint32_t* bits;          // run's hull words of this column (stride 32 words per block), block blk0 first
     const uint8_t* rec_x;
@@ -127,15 +151,16 @@ struct HullRunMergeCtx {
     int blk0;
     __device__ __forceinline__ uint32_t h_ld(int b) const { return bits[(b - blk0) * 32]; }
     __device__ __forceinline__ void h_st(int b, uint32_t v) { bits[(b - blk0) * 32] = v; }
-    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_x + (unsigned)r * rs32); }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return g_load<WIDE>(rec_x + (unsigned)r * rs32); }
 };
 
 // CTA = kHullWarps column groups x nsub sub-runs. Each warp builds the hull of its sub-run alone; then one warp per
 // group repairs the nsub-1 junctions inside the run, looking only at the run's own rows (triples that reach across
 // a run boundary are the merge kernel's), and the words go out. Splitting the run shortens the chain of dependent
 // pushes per warp, which is what a small band's pass 2 waits for.
-template <int NSUB>
+template <int NSUB, bool WIDE>
 __device__ __forceinline__ void hull_build_body(const HullParams p) {
+    constexpr int kG = (int)sizeof(typename GVal<WIDE>::T);
     extern __shared__ __align__(16) uint8_t s_hull[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int cgi = warp & (kHullWarps - 1), sub = NSUB > 1 ? warp / kHullWarps : 0;
@@ -153,11 +178,11 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
     int lag = p.L;
     asm volatile("" : "+r"(lag));
     if (active && s0 < s1) {
-        uint8_t* stage = s_hull + (size_t)kHullWarps * p.pb * 128 + (size_t)warp * 2048;
-        HullBuildCtx c;
+        uint8_t* stage = s_hull + (size_t)kHullWarps * p.pb * 128 + (size_t)warp * 2 * HullBuildCtx<WIDE>::kSlot;
+        HullBuildCtx<WIDE> c;
         c.gst = stage; c.gst_s = smem_u32(stage);
         c.bits = gbits + (s0 - b0) * 32;
-        c.rec0 = recbase + cg * 32; c.rec_lane = c.rec0 + lane; c.cls0 = recbase + p.wp + cg * 4;
+        c.rec0 = recbase + cg * 32 * kG; c.rec_lane = c.rec0 + lane * kG; c.cls0 = recbase + p.cls_off + cg * 4;
         c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
         c.clst0 = p.clsT + (long long)img * p.nblk * p.wc + cg * 32 + lane; c.wc = p.wc;
         c.rs = p.rs; c.rs32 = (unsigned)p.rs;
@@ -165,16 +190,16 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
         c.vm = ncol >= 32 ? 0xFFFFFFFFu : ((1u << ncol) - 1u);
         c.nrows = p.buf_rows; c.lane = lane; c.ncg = p.ncg; c.cur_blk = 0; c.slot = 0;
         c.blk_first = s0; c.blk_end = s1;
-        HullBuild<HullBuildCtx> hb(c, lag);
+        HullBuild<HullBuildCtx<WIDE>, WIDE> hb(c, lag);
         hb.run(s0, s1, p.buf_rows);
     }
     if (NSUB > 1) {
         __syncthreads();
         if (active && sub == 0 && cg * 32 + lane < p.w) {
-            HullRunMergeCtx m;
-            m.bits = gbits; m.rec_x = recbase + cg * 32 + lane; m.rs32 = (unsigned)p.rs; m.blk0 = b0;
+            HullRunMergeCtx<WIDE> m;
+            m.bits = gbits; m.rec_x = recbase + (cg * 32 + lane) * kG; m.rs32 = (unsigned)p.rs; m.blk0 = b0;
             const int hi = (b1 * 32 < p.buf_rows ? b1 * 32 : p.buf_rows) - 1;
-            HullMerge<HullRunMergeCtx> hm(m, lag, b0 * 32, hi);
+            HullMerge<HullRunMergeCtx<WIDE>, WIDE> hm(m, lag, b0 * 32, hi);
             for (int j = b0 + p.sb; j < b1; j += p.sb) hm.junction(j * 32);
         }
         __syncthreads();
@@ -185,36 +210,43 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
     }
 }
 
-__global__ void __launch_bounds__(kHullWarps * 32, 10) hull_build_kernel(HullParams p) { hull_build_body<1>(p); }
-__global__ void __launch_bounds__(kHullWarps * 32 * 4, 2) hull_build4_kernel(HullParams p) { hull_build_body<4>(p); }
+template <bool WIDE>
+__global__ void __launch_bounds__(kHullWarps * 32, WIDE ? 8 : 10) hull_build_kernel(HullParams p) { hull_build_body<1, WIDE>(p); }
+template <bool WIDE>
+__global__ void __launch_bounds__(kHullWarps * 32 * 4, 2) hull_build4_kernel(HullParams p) { hull_build_body<4, WIDE>(p); }
 
+template <bool WIDE>
 struct HullMergeCtx {
     uint32_t* hcol;          // hull word of block 0 of this column (stride wc per block)
-    const uint8_t* rec_x;    // g8 of buffer row 0 of this column
+    const uint8_t* rec_x;    // row distance of buffer row 0 of this column
     unsigned rs32;
     int wc;
     __device__ __forceinline__ uint32_t h_ld(int b) const { return hcol[(long long)b * wc]; }
     __device__ __forceinline__ void h_st(int b, uint32_t v) { hcol[(long long)b * wc] = v; }
-    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_x + (unsigned)r * rs32); }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return g_load<WIDE>(rec_x + (unsigned)r * rs32); }
 };
 
+template <bool WIDE>
 __global__ void __launch_bounds__(256) hull_merge_kernel(HullParams p) {
+    constexpr int kG = (int)sizeof(typename GVal<WIDE>::T);
     const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
     if (t >= (long long)p.n_img * p.w) return;
     const int img = (int)(t / p.w), x = (int)(t - (long long)img * p.w);
-    HullMergeCtx c;
+    HullMergeCtx<WIDE> c;
     c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
-    c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x;
+    c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x * kG;
     c.rs32 = (unsigned)p.rs; c.wc = p.wc;
-    HullMerge<HullMergeCtx> hm(c, p.L, p.buf_rows);
+    HullMerge<HullMergeCtx<WIDE>, WIDE> hm(c, p.L, p.buf_rows);
     for (int b = p.pb; b < p.nblk; b += p.pb) hm.junction(b * 32);
 }
 
-// A junction only ever touches sites within 2L rows of itself, so junctions >= 4L rows apart can be repaired at
-// the same time: nphase = ceil(4L / run length) launches, launch i takes every nphase-th junction. Any order of
+// A junction only ever touches sites within 2L rows of itself, so junctions far enough apart can be repaired at
+// the same time: hull_merge_phases(L, run blocks) launches, launch i takes every nphase-th junction. Any order of
 // repairs ends in the same kind of hull (each pop re-tests both triples around the adjacency it creates).
 // thread = (junction, column).
+template <bool WIDE>
 __global__ void __launch_bounds__(256) hull_merge_par_kernel(HullParams p) {
+    constexpr int kG = (int)sizeof(typename GVal<WIDE>::T);
     const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
     const int njun = p.nruns_b - 1;                       // junctions 1 .. njun (junction k is at block k*pb)
     const int nmine = (njun - p.merge_phase + p.merge_nphase - 1) / p.merge_nphase;  // k = 1 + phase + i*nphase
@@ -223,11 +255,11 @@ __global__ void __launch_bounds__(256) hull_merge_par_kernel(HullParams p) {
     const int img = (int)(t / per_img);
     const long long r = t - (long long)img * per_img;
     const int k = 1 + p.merge_phase + p.merge_nphase * (int)(r / p.w), x = (int)(r % p.w);
-    HullMergeCtx c;
+    HullMergeCtx<WIDE> c;
     c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
-    c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x;
+    c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x * kG;
     c.rs32 = (unsigned)p.rs; c.wc = p.wc;
-    HullMerge<HullMergeCtx> hm(c, p.L, p.buf_rows);
+    HullMerge<HullMergeCtx<WIDE>, WIDE> hm(c, p.L, p.buf_rows);
     hm.junction(k * p.pb * 32);
 }
 

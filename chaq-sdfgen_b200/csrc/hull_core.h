@@ -31,7 +31,7 @@
 // minimum anywhere (removal is by two sites that stay or are themselves removed later by the same rule).
 //
 // The hull is one bit per pixel, word (32-row block b, column x); g8 is re-read from pass 1's record whenever
-// a site's height is needed again. All int32: spans <= 1024 rows, heights <= 2^16 -> |terms| < 2^29.
+// a site's height is needed again.
 // The same source is compiled by g++ in tests/emul (checked against the oracle) and by nvcc.
 #pragma once
 #include <stdint.h>
@@ -43,24 +43,19 @@ constexpr int kFarRow = 1 << 28;  // "no such row"; survives +- image-size arith
 #define CQ_UNLIKELY(x) __builtin_expect(!!(x), 0)
 
 
-#ifndef CQ_HULL_WIDE
-constexpr int kHullMaxPieceBlocks = 32;  // build runs are at most 1024 rows (int32 range of the domination test)
-
-// site b is never the minimum between its neighbours a < b < c (cross-multiplied df.c:67)
+// site b is never the minimum between its neighbours a < b < c (cross-multiplied df.c:67).
+// WIDE = false: int32 (|terms| < 2^29 while spans stay <= 1024 rows and heights <= 2^16: the spreads <= 256 of the
+// byte-wide intermediate). WIDE = true: 64-bit, for row distances up to 1024 (16-bit intermediate) and longer runs.
+template <bool WIDE>
 CQ_HD bool cq_dominated(int ap, int ah, int bp, int bh, int cp, int ch) {
+    if (WIDE) {
+        const long long u = bp - ap, w = cp - bp;
+        return w * (bh - ah) - u * (ch - bh) >= u * w * (u + w);
+    }
     const int u = bp - ap, w = cp - bp;
     return w * (bh - ah) - u * (ch - bh) >= u * w * (u + w);
 }
-#else
-// Wide variant (not compiled into the library yet; tests/emul builds it to check the organisation for L up to 1024,
-// i.e. spreads beyond the banded path): u*w*(u+w) passes 2^31 once spans reach ~1300 rows, so the test is 64-bit,
-// and runs may be longer.
-constexpr int kHullMaxPieceBlocks = 128;
-CQ_HD bool cq_dominated(int ap, int ah, int bp, int bh, int cp, int ch) {
-    const long long u = bp - ap, w = cp - bp;
-    return w * (bh - ah) - u * (ch - bh) >= u * w * (u + w);
-}
-#endif
+constexpr int hull_max_run_blocks(bool wide) { return wide ? 128 : 32; }  // rows per build run / 32
 
 // ---------------------------------------------------------------------------------------------------------
 // build. Ctx provides:
@@ -70,7 +65,7 @@ CQ_HD bool cq_dominated(int ap, int ah, int bp, int bh, int cp, int ch) {
 //   uint32_t g_row(int r)                 g8 of buffer row r (any row of this run)
 //   uint32_t bits_ld(int i) / void bits_st(int i, uint32_t)   hull word of block b0 + i of this run
 //   void     block_end(int blk, uint32_t word)                 the block's pushes are done (word = its hull bits now)
-template <class Ctx>
+template <class Ctx, bool WIDE = false>
 struct HullBuild {
     Ctx& c;
     int L, b0, pblk;
@@ -116,7 +111,7 @@ struct HullBuild {
         const int g8 = (int)c.g_push(j);
         if (g8 < L) {
             const int h = (g8 + 1) * (g8 + 1);
-            while (sec_p >= 0 && cq_dominated(sec_p, sec_h, top_p, top_h, rr, h)) pop();
+            while (sec_p >= 0 && cq_dominated<WIDE>(sec_p, sec_h, top_p, top_h, rr, h)) pop();
             hwp |= 1u << j;
             thr_p = sec_p; thr_h = sec_h;
             sec_p = top_p; sec_h = top_h;
@@ -154,7 +149,7 @@ CQ_HD int hull_merge_phases(int L, int pb) {
 // ---------------------------------------------------------------------------------------------------------
 // merge. Ctx provides: uint32_t h_ld(int blk) / void h_st(int blk, uint32_t) (this column's hull words, all
 // blocks of the buffer) and uint32_t g_row(int r).
-template <class Ctx>
+template <class Ctx, bool WIDE = false>
 struct HullMerge {
     Ctx& c;
     int L;
@@ -208,7 +203,7 @@ struct HullMerge {
                 u2 = down(u1 - 1, cq_max(lo_row, d1 - span));
                 if (u2 >= 0) u2h = height(u2);
             }
-            if (u2 >= 0 && cq_dominated(u2, u2h, u1, u1h, d1, d1h)) {
+            if (u2 >= 0 && cq_dominated<WIDE>(u2, u2h, u1, u1h, d1, d1h)) {
                 clear(u1);
                 u1 = u2; u1h = u2h; u2 = -2;
                 if (d2 >= 0 && d2 - u1 > span) d2 = -1;
@@ -218,7 +213,7 @@ struct HullMerge {
                 d2 = up(d1 + 1, cq_min(hi_row, u1 + span));
                 if (d2 >= 0) d2h = height(d2);
             }
-            if (d2 >= 0 && cq_dominated(u1, u1h, d1, d1h, d2, d2h)) {
+            if (d2 >= 0 && cq_dominated<WIDE>(u1, u1h, d1, d1h, d2, d2h)) {
                 clear(d1);
                 d1 = d2; d1h = d2h; d2 = -2;
                 if (u2 >= 0 && d1 - u2 > span) u2 = -1;

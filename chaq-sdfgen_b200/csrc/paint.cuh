@@ -20,6 +20,7 @@ constexpr int kPaintSegWords = 33;  // owners of one block per lane: at most one
 
 __host__ __device__ inline size_t hull_paint_smem() { return kTableBytes + (size_t)kEmitWarps * kPaintSegWords * 128; }
 
+template <bool WIDE>
 struct HullPaintCtx {
     const uint32_t* hcol;    // hull word of block 0 of this column (stride wc per block)
     const uint32_t* clst;    // transposed class word of block 0 of this column (stride wc per block)
@@ -38,7 +39,7 @@ struct HullPaintCtx {
     int qcls, qm, qlo, qhi, qbyte, qsign;
 
     __device__ __forceinline__ uint32_t h_ld(int b) const { return b < nblk ? __ldg(hcol + (long long)b * wc) : 0u; }
-    __device__ __forceinline__ uint32_t g_row(int r) const { return __ldg(rec_lane + (unsigned)r * rs32); }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return g_load<WIDE>(rec_lane + (unsigned)r * rs32); }
     __device__ __forceinline__ uint32_t cls_t(int b) const {
         const uint32_t w = __ldg(clst + (long long)(b < nblk ? b : nblk - 1) * wc);
         return b < nblk ? w : (uint32_t)((int32_t)w >> 31);  // past the buffer: the class of the last row (bit 31 of the last word)
@@ -113,6 +114,7 @@ struct HullPaintCtx {
     }
 };
 
+template <bool WIDE>
 __global__ void __launch_bounds__(kEmitWarps * 32, 8) hull_paint_kernel(HullParams p) {
     extern __shared__ __align__(16) uint8_t s_hull[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -131,11 +133,11 @@ __global__ void __launch_bounds__(kEmitWarps * 32, 8) hull_paint_kernel(HullPara
     y0 = y0 > p.out_begin ? y0 : p.out_begin;
     y1 = y1 < p.out_end ? y1 : p.out_end;
     if (y0 >= y1) return;
-    HullPaintCtx c;
+    HullPaintCtx<WIDE> c;
     const int x = cg * 32 + lane;
     c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
     c.clst = p.clsT + (long long)img * p.nblk * p.wc + x;
-    c.rec_lane = p.inter + (long long)img * p.buf_rows * p.rs + x;
+    c.rec_lane = p.inter + (long long)img * p.buf_rows * p.rs + x * (int)sizeof(typename GVal<WIDE>::T);
     c.flag0 = p.flags + (long long)img * p.nblk * p.ncg + cg;
     c.seg = reinterpret_cast<uint32_t*>(s_hull + kTableBytes + (size_t)warp * kPaintSegWords * 128) + lane;
     c.rs32 = (unsigned)p.rs; c.wc = p.wc; c.ncg = p.ncg; c.nblk = p.nblk; c.lane = lane;
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(kEmitWarps * 32, 8) hull_paint_kernel(HullPara
     c.qcls = -1; c.qm = 1; c.qlo = 0; c.qhi = 0x7fffffff; c.qbyte = 0; c.qsign = 1; c.qthr = s_thr;
     int lag = p.L;
     asm volatile("" : "+r"(lag));
-    HullPaint<HullPaintCtx> hp(c, lag, p.c2);
+    HullPaint<HullPaintCtx<WIDE>> hp(c, lag, p.c2);
     hp.run(y0, y1);
 }
 

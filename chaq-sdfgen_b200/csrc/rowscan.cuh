@@ -8,6 +8,8 @@
 // Output: uint16 per pixel, bit 15 = class (1 = inside, the reference's `true`), bits 0..14 = min(distance
 // along the row to the nearest pixel of the other class, cap). No transposed store (df.c:92): the second
 // pass walks columns with adjacent threads on adjacent columns instead.
+// Record mode (RowScanParams::record, spreads 257..1024 of the banded path): per row [wp x uint16 min(G, cap) - 1 |
+// wp/8 bytes of class bits], the 16-bit sibling of rowscan8.cuh's record, read by the hull kernels (hull.cuh, WIDE).
 //
 // Mapping: one warp per row. Phase A turns the row into a bit string in shared memory (16 pixels per lane
 // per 128-bit load on the fast path, ballot on the generic path). Phase B gives each lane one 32-pixel
@@ -38,6 +40,9 @@ struct RowScanParams {
     int above;
     int cap;
     int nwords;  // ceil(w/32)
+    int record;          // 0: [rows][w] uint16 with the class in bit 15; 1: records (below)
+    int wp;              // record mode: w rounded up to 128
+    long long rs_bytes;  // record mode: bytes per record = 2*wp + wp/8
 };
 
 __global__ void __launch_bounds__(kRowWarps * 32) rowscan_kernel(RowScanParams p) {
@@ -79,7 +84,13 @@ __global__ void __launch_bounds__(kRowWarps * 32) rowscan_kernel(RowScanParams p
 
     // ---------------- phase B: distances ----------------
     const int cap = p.cap;
-    uint16_t* dst = p.inter + (size_t)row * (size_t)w;
+    const bool rec = p.record != 0;
+    uint8_t* recbase = reinterpret_cast<uint8_t*>(p.inter) + (size_t)row * (size_t)p.rs_bytes;
+    uint16_t* dst = rec ? reinterpret_cast<uint16_t*>(recbase) : p.inter + (size_t)row * (size_t)w;
+    if (rec) {  // class words of the row, as rowscan8 leaves them
+        uint32_t* crec = reinterpret_cast<uint32_t*>(recbase + 2 * (size_t)p.wp);
+        for (int wi = lane; wi < p.nwords; wi += 32) crec[wi] = bits[wi];
+    }
     const bool vec_ok = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
     const uint32_t lt = (1u << lane) - 1u, gt = lane == 31 ? 0u : (0xFFFFFFFEu << lane);
     int carry0 = -kFar, carry1 = -kFar;  // last pixel of class 0 / 1 in earlier chunks
@@ -151,14 +162,14 @@ __global__ void __launch_bounds__(kRowWarps * 32) rowscan_kernel(RowScanParams p
                 const bool valid = b < nvalid;
                 int dr = c ? y0 : y1;
                 int m = min(min(dl[b], dr), cap);
-                uint32_t o = (c ? 0x8000u : 0u) | (uint32_t)m;
+                uint32_t o = rec ? (uint32_t)((valid ? m : cap) - 1) : ((c ? 0x8000u : 0u) | (uint32_t)m);
                 if (b & 1) packed[b >> 1] = o << 16; else packed[b >> 1] |= o;
                 if (valid) {
                     y0 = c ? y0 + 1 : 1;
                     y1 = c ? 1 : y1 + 1;
                 }
             }
-            if (nvalid == 32 && vec_ok) {
+            if ((nvalid == 32 || rec) && vec_ok) {  // a record has room for the whole last word (padding: nothing in reach)
                 uint4* d4 = reinterpret_cast<uint4*>(dst + x0);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)

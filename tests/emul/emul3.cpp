@@ -14,14 +14,9 @@
 
 using namespace chaq;
 
-// -DCQ_HULL_WIDE: the same organisation with a 16-bit row distance and the 64-bit domination test, for L up to 1024
-#ifdef CQ_HULL_WIDE
+// wide = 1: the same organisation with a 16-bit row distance and the 64-bit domination test, for L up to 1024
 typedef uint16_t gval_t;
-static const int kMaxCap = 1025;
-#else
-typedef uint8_t gval_t;
-static const int kMaxCap = 256;
-#endif
+static int g_max_cap = 256;
 
 static void rowscan_naive(const uint8_t* mask, int w, int h, int C, std::vector<gval_t>& g8) {
     g8.resize((size_t)w * h);
@@ -43,7 +38,7 @@ struct Col {
     std::vector<uint32_t>* H;   // hull words of this column
     std::vector<uint8_t>* Q;    // block flags of this column (the "group" is this one column)
     long oob = 0;
-    uint32_t g_row(int r) { if (r < 0 || r >= nrows) { ++oob; return kMaxCap - 1; } return g[(size_t)r * stride]; }
+    uint32_t g_row(int r) { if (r < 0 || r >= nrows) { ++oob; return g_max_cap - 1; } return g[(size_t)r * stride]; }
 };
 
 struct BuildCtx : Col {
@@ -114,14 +109,16 @@ extern "C" void emul3_paint_stats(long* live, long* dead) { *live = g_live; *dea
 // merge_order 0: junctions top to bottom; 1: in hull_merge_phases(L, run blocks) rounds, round i taking every
 // nphase-th junction (what the parallel merge kernel does; same-round junctions must never store the same hull
 // word -- rc 2500 if they do).
-extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int asym, int build_blocks, int emit_rows,
-                         int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order, int nsub) {
+template <bool WIDE>
+static int emul3_run(const uint8_t* mask, int w, int h, size_t spread, int asym, int build_blocks, int emit_rows,
+                     int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order, int nsub) {
+    g_max_cap = WIDE ? 1025 : 256;
     QuantTable q; build_quant_table(spread, asym, &q);
     LevelTable lt; build_level_table(q, &lt);
     const int C = lt.cap_eff, L = C - 1;
     if (cap_eff) *cap_eff = C;
-    if (C > kMaxCap) return 1;
-    if (build_blocks < 1 || build_blocks > kHullMaxPieceBlocks) return 3;
+    if (C > g_max_cap) return 1;
+    if (build_blocks < 1 || build_blocks > hull_max_run_blocks(WIDE)) return 3;
     std::vector<gval_t> g8;
     rowscan_naive(mask, w, h, C, g8);
     const int nblk = (h + 31) / 32;
@@ -139,7 +136,7 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
                 c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
                 const int s1 = s0 + sb < b1 ? s0 + sb : b1;
                 c.b0 = s0; c.bits.assign(s1 - s0, 0xdeadbeefu);
-                HullBuild<BuildCtx> hb(c, L);
+                HullBuild<BuildCtx, WIDE> hb(c, L);
                 hb.run(s0, s1, h);
                 for (int b = s0; b < s1; ++b) H[b] = c.bits[b - s0];
                 if (c.oob) return 1000;
@@ -148,7 +145,7 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
                 MergeCtx c;
                 c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
                 const int hi = (b1 * 32 < h ? b1 * 32 : h) - 1;
-                HullMerge<MergeCtx> hm(c, L, b0 * 32, hi);
+                HullMerge<MergeCtx, WIDE> hm(c, L, b0 * 32, hi);
                 for (int s0 = b0 + sb; s0 < b1; s0 += sb) hm.junction(s0 * 32);
                 if (c.oob) return 1500;
             }
@@ -156,7 +153,7 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
         {
             MergeCtx c;
             c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
-            HullMerge<MergeCtx> hm(c, L, h);
+            HullMerge<MergeCtx, WIDE> hm(c, L, h);
             if (merge_order == 1) {
                 const int nphase = hull_merge_phases(L, build_blocks);
                 std::vector<int> writer(nblk);
@@ -192,4 +189,13 @@ extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int a
         }
     }
     return 0;
+}
+
+extern "C" int emul3_sdf(const uint8_t* mask, int w, int h, size_t spread, int asym, int build_blocks, int emit_rows,
+                         int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order, int nsub) {
+    return emul3_run<false>(mask, w, h, spread, asym, build_blocks, emit_rows, y_begin, y_end, out, cap_eff, merge_order, nsub);
+}
+extern "C" int emul3_sdf_wide(const uint8_t* mask, int w, int h, size_t spread, int asym, int build_blocks, int emit_rows,
+                              int y_begin, int y_end, uint8_t* out, int* cap_eff, int merge_order, int nsub) {
+    return emul3_run<true>(mask, w, h, spread, asym, build_blocks, emit_rows, y_begin, y_end, out, cap_eff, merge_order, nsub);
 }

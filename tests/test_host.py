@@ -299,6 +299,7 @@ def _build_emul3(tmp_path_factory, name, *defines):
     u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
     L.emul3_sdf.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p,
                             C.POINTER(C.c_int), C.c_int, C.c_int]
+    L.emul3_sdf_wide.argtypes = L.emul3_sdf.argtypes
     return L
 
 
@@ -307,10 +308,16 @@ def emul3(tmp_path_factory):
     return _build_emul3(tmp_path_factory, "emul3")
 
 
+class _Wide:
+    """The wide instantiation of the same library (16-bit row distances, 64-bit domination test, L <= 1024)."""
+
+    def __init__(self, L):
+        self.emul3_sdf = L.emul3_sdf_wide
+
+
 @pytest.fixture(scope="session")
-def emul3_wide(tmp_path_factory):
-    """hull_core.h with -DCQ_HULL_WIDE: 16-bit row distances, 64-bit domination test, longer class ring (L <= 1024)."""
-    return _build_emul3(tmp_path_factory, "emul3w", "-DCQ_HULL_WIDE")
+def emul3_wide(emul3):
+    return _Wide(emul3)
 
 
 def _emul3_u8(L, mask, spread, asym, build_blocks, emit_rows, y0=0, y1=None, order=None, nsub=1):
