@@ -118,6 +118,78 @@ def syn_glyphs(count, n=256, first=0):
     return imgs
 
 
+def syn_discs_device(n, device, seed=88172645463325252, n_discs=200):
+    """SYN-DISCS(n) built on the device (same integer test as syn_discs: (x-cx)^2 + (y-cy)^2 <= r^2), for sizes at
+    which the numpy loop is slow. tests/test_gpu_parity.py checks it against syn_discs."""
+    import torch
+    M = (1 << 64) - 1
+    s = seed
+
+    def rnd():
+        nonlocal s
+        s ^= (s << 13) & M
+        s ^= s >> 7
+        s ^= (s << 17) & M
+        return s
+
+    img = torch.zeros((n, n), dtype=torch.uint8, device=device)
+    for _ in range(n_discs):
+        cx, cy = rnd() % n, rnd() % n
+        r = 8 + rnd() % max(n // 16, 1)
+        y0, y1, x0, x1 = max(0, cy - r), min(n - 1, cy + r), max(0, cx - r), min(n - 1, cx + r)
+        ys = torch.arange(y0, y1 + 1, device=device, dtype=torch.int64)[:, None]
+        xs = torch.arange(x0, x1 + 1, device=device, dtype=torch.int64)[None, :]
+        inside = ((xs - cx) ** 2 + (ys - cy) ** 2) <= r * r
+        img[y0:y1 + 1, x0:x1 + 1].masked_fill_(inside, 255)
+    return img
+
+
+def other_configs(pkg, dev):
+    """The other BASELINE configs on one GPU, device-timed (min of a few runs, CUDA events; inputs resident): parity
+    cases (tests/test_gpu_parity.py checks each against the oracle), carried here so that the driver's record has them."""
+    import torch
+
+    def timed(fn, iters):
+        fn()
+        fn()
+        torch.cuda.synchronize()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+        for a, b in ev:
+            a.record()
+            fn()
+            b.record()
+        torch.cuda.synchronize()
+        return min(a.elapsed_time(b) for a, b in ev)
+
+    res = {}
+    try:
+        n, spread = 4096, 64
+        d = torch.from_numpy(syn_discs(n)).to(dev)
+        out = torch.empty((n, n), dtype=torch.uint8, device=dev)
+        ws = torch.empty(pkg.workspace_bytes(n, n, spread), dtype=torch.uint8, device=dev)
+        ms = timed(lambda: pkg.sdf_u8_device(d, n, n, spread=spread, out=out, workspace=ws), 10)
+        res["config2"] = {"workload": "SYN-DISCS(4096), spread 64", "ms": ms, "Mpix/s": n * n / ms / 1e3}
+        n, s, spread = 4096, 256, 16
+        d = torch.from_numpy(syn_glyphs(n, s)).to(dev)
+        out = torch.empty((n, s, s), dtype=torch.uint8, device=dev)
+        ws = torch.empty(pkg.workspace_bytes(s, s, spread, n), dtype=torch.uint8, device=dev)
+        ms = timed(lambda: pkg.sdf_u8_batched_device(d, n, s, s, spread=spread, out=out, workspace=ws), 10)
+        res["config3"] = {"workload": "4096 x SYN-GLYPH 256x256, spread 16, one batched call (fused small-image kernel)",
+                          "ms": ms, "Mpix/s": n * s * s / ms / 1e3, "GB/s_of_2_B_per_px": 2 * n * s * s / ms / 1e6}
+        del d, out, ws
+        n, spread = 32768, 1024
+        d = syn_discs_device(n, dev)
+        out = torch.empty((n, n), dtype=torch.uint8, device=dev)
+        ws = torch.empty(pkg.workspace_bytes(n, n, spread), dtype=torch.uint8, device=dev)
+        ms = timed(lambda: pkg.sdf_u8_device(d, n, n, spread=spread, out=out, workspace=ws), 3)
+        res["config5"] = {"workload": "SYN-DISCS(32768), spread 1024, one GPU", "ms": ms, "Mpix/s": n * n / ms / 1e3}
+        del d, out, ws
+        torch.cuda.empty_cache()
+    except Exception as ex:  # noqa: BLE001 -- extra information only; the headline line must still print
+        res["error"] = repr(ex)
+    return res
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -191,12 +263,13 @@ def run_reference(args, rank, world):
     est_full = probe[0] * (SIDE / min(4096, SIDE)) ** 2
     while side > 4096 and est_full * (side / SIDE) ** 2 > 12.0:
         side //= 2
-    ts, threads = cpu_reference_run(img, side, SPREAD, args.steps, min(args.warmup, 1))
+    warm = min(args.warmup, 1)  # one warm-up of a multi-second CPU step is enough; the line says what was done
+    ts, threads = cpu_reference_run(img, side, SPREAD, args.steps, warm)
     t = float(np.mean(ts))
     mpix = side * side / t / 1e6
     sample = f"{side}x{side} top-left crop of the workload per step" if side != SIDE else "the full workload per step"
     line = {"impl": "reference", "metric": "SDF Mpix/s (inside+outside)", "value": mpix, "unit": "Mpix/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": warm, "ms_per_step": t * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "sample": sample},
             "cpu_baseline": {"value": mpix, "unit": "Mpix/s", "cores": threads, "kind": "reference", "sample": sample},
@@ -284,10 +357,32 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t[0].item())
         phases = {"rowscan_ms": float(t[1]), "halo_exchange_ms": float(t[2]), "envelope_ms": float(t[3]),
+                  "rank0_pass2_kernels_ms": None,
                   "halo": state.get("halo"), "note": "per-phase CUDA-event means, max over ranks; halo 'peer' = pairwise "
                   "device-side signals + copies out of the neighbours' peer-mapped buffers over NVLink, 'p2p' = NCCL send/recv"}
     ms_step = ms_total / K
     value = h * w / (ms_step * 1e-3) / 1e6
+    parity_vs_n1 = None
+    sharded_kernel_ms = None
+    if dist is not None:
+        # outside the timed region: every rank also runs the WHOLE image alone and compares its band, byte for byte
+        whole = torch.from_numpy(img).to(dev)
+        ref_out = pkg.sdf_u8_device(whole, w, h, spread=SPREAD)
+        same = torch.equal(res, ref_out[r0:r1])
+        flag = torch.tensor([1 if same else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        parity_vs_n1 = bool(flag.item())
+        del whole, ref_out
+        # per-kernel times of one rank's pass 2 (library CUDA events), a few extra steps
+        if rank == 0:
+            pkg.profile_enable(True)
+        for _ in range(5):
+            step()
+        torch.cuda.synchronize()
+        if rank == 0:
+            sharded_kernel_ms = pkg.profile_mean_ms()
+            pkg.profile_enable(False)
+        dist.barrier()
 
     # ---- end to end through the host-buffer C-ABI call (pinned host memory; H2D + kernels + D2H timed) ----
     Ke = max(3, min(K, 10))
@@ -365,11 +460,15 @@ def run_ours(args, rank, world, local_rank):
             "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "sharding": f"row bands x{world}" + (", halo exchange of spread rows of the "
-                       "1.125 B/px intermediate (NCCL p2p)" if world > 1 else ""),
+                       f"1.125 B/px intermediate ({'pull over peer-mapped memory' if state.get('halo') == 'peer' else 'NCCL send/recv'})"
+                       if world > 1 else ""),
                        "l2": "inputs larger than L2 (268 MB mask + 302 MB intermediate + 268 MB bitmap per step vs "
                              "126 MB L2)"},
             "roofline": roofline, "passes": passes, "phases": phases, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks}
+            "clocks": clocks, "parity_vs_n1": parity_vs_n1,
+            "other_configs": other_configs(pkg, dev) if world == 1 and SIDE == 16384 and not os.environ.get("CHAQ_BENCH_SKIP_OTHER") else None}
+    if phases is not None:
+        phases["rank0_pass2_kernels_ms"] = sharded_kernel_ms
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
