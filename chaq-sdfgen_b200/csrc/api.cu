@@ -375,7 +375,10 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     if (nsub == 4 && p.pb < 8 && g_tuning.hull_pb <= 0) { p.pb = 8; p.nruns_b = (p.nblk + p.pb - 1) / p.pb; }  // sub-runs of >= 2 blocks
     p.sb = (p.pb + (int)nsub - 1) / (int)nsub; p.nsub = (int)nsub;
     const int bfirst = p.out_begin >> 5, nbo = ((p.out_end - 1) >> 5) - bfirst + 1;
-    long long eb = (strips * nbo + target - 1) / target;
+    // paint runs: starting one is cheap (the cursor is found by a local search), so short runs -- more CTAs than the
+    // build, evening out dense and empty areas -- win: ~8 blocks at 16384^2
+    const long long target_e = (long long)di.sms * 56;
+    long long eb = (strips * nbo + target_e - 1) / target_e;
     eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
     if (g_tuning.hull_eb > 0) eb = g_tuning.hull_eb;
     if (eb < 1) eb = 1;

@@ -107,12 +107,10 @@ struct HullBuild {
         sec_p = thr_p; sec_h = thr_h;
         thr_p = -2;
     }
-    CQ_HD void push(int rr, int j) {
-        const int g8 = (int)c.g_push(j);
-        if (g8 < L) {
-            const int h = (g8 + 1) * (g8 + 1);
+    CQ_HD void push(int rr, int h) {
+        {
             while (sec_p >= 0 && cq_dominated<WIDE>(sec_p, sec_h, top_p, top_h, rr, h)) pop();
-            hwp |= 1u << j;
+            hwp |= 1u << (rr & 31);
             thr_p = sec_p; thr_h = sec_h;
             sec_p = top_p; sec_h = top_h;
             top_p = rr; top_h = h;
@@ -127,8 +125,27 @@ struct HullBuild {
             hwp = 0u;
             c.block_begin(blk);
             if (!c.block_quiet(L)) {
+                // A site that lies on or above the chord of its two row neighbours (both sites) is never the strict
+                // minimum anywhere: 2 h_j >= h_{j-1} + h_{j+1} + 2 with h = G^2 (the domination test for u = w = 1).
+                // It would be popped by the very next push; not pushing it saves the push and the pop. Whether the
+                // neighbours themselves end up on the hull does not matter (a point above a chord of input points is
+                // not a vertex of their lower hull). Rows at the ends of a block are always pushed.
                 const int jn = cq_min(32, nrows - blk * 32);
-                for (int j = 0; j < jn; ++j) push(blk * 32 + j, j);
+                const int big = 1 << 24;  // "no site": never a dominator, never pushed
+                int hp = big, hc, hn;
+                {
+                    const int g0 = (int)c.g_push(0);
+                    hc = g0 < L ? (g0 + 1) * (g0 + 1) : big;
+                }
+                for (int j = 0; j < jn; ++j) {
+                    hn = big;
+                    if (j + 1 < jn) {
+                        const int g1 = (int)c.g_push(j + 1);
+                        hn = g1 < L ? (g1 + 1) * (g1 + 1) : big;
+                    }
+                    if (hc < big && !(2 * hc >= hp + hn + 2)) push(blk * 32 + j, hc);
+                    hp = hc; hc = hn;
+                }
             }
             c.bits_st(blk - b0, hwp);
             c.block_end(blk, hwp);

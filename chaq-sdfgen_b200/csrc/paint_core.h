@@ -118,6 +118,48 @@ struct HullPaint {
             ehw = c.h_ld(eblk);
         }
     }
+    // highest site in [lo, from], or -1
+    CQ_HD int prev_site(int from, int lo) {
+        if (from < lo) return -1;
+        int b = from >> 5;
+        const int bend = lo >> 5;
+        uint32_t bits = c.h_ld(b) & (0xFFFFFFFFu >> (31 - (from & 31)));
+        for (;;) {
+            if (b == bend) bits &= (0xFFFFFFFFu << (lo & 31));
+            if (bits) return (b << 5) + cq_highbit(bits);
+            if (b == bend) return -1;
+            --b;
+            bits = c.h_ld(b);
+        }
+    }
+    // Where the walk stands when it reaches row y0. Walking down from y0 - L would visit every site in between (about
+    // L/6 of them on shapes, each a dependent load); the hull is proper inside any window of 2L+1 rows, so the values
+    // its sites take at row y0 fall and then rise along the hull: start at the site nearest above y0 and climb only
+    // while the site before is strictly better. Sites below y0 are plan()'s business (it moves on while the successor
+    // is at least as good).
+    CQ_HD void start_cursor(int y0) {
+        const int lo = cq_max(y0 - L, 0);
+        cur_p = -1; cur_g = kPaintNoSite; nxt_p = -1; nxt_g = 0;
+        int s = prev_site(y0, lo);
+        if (s < 0) {  // nothing within reach above: the cursor stands before the first site below y0
+            const int t = y0 + 1;
+            eblk = t >> 5;
+            ehw = c.h_ld(eblk) & (0xFFFFFFFFu << (t & 31));
+            return;
+        }
+        int sg = (int)c.g_row(s) + 1;
+        for (;;) {
+            const int q = prev_site(s - 1, lo);
+            if (q < 0) break;
+            const int qg = (int)c.g_row(q) + 1;
+            const int ds = y0 - s, dq = y0 - q;
+            if (!(dq * dq + qg * qg < ds * ds + sg * sg)) break;
+            s = q; sg = qg;
+        }
+        cur_p = s; cur_g = sg;
+        eblk = s >> 5;
+        ehw = (s & 31) == 31 ? 0u : (c.h_ld(eblk) & (0xFFFFFFFEu << (s & 31)));
+    }
     static CQ_HD uint32_t pack(int rel, int g) { return ((uint32_t)(rel + kPaintRelBias) << 16) | (uint32_t)g; }
 
     // owners of rows [r0, r1) of the block that starts at row Y. Entry 0 of the list is the owner of r0.
@@ -198,13 +240,8 @@ struct HullPaint {
             const int n = cls_up(y0 + 1, lastknown, ecls);
             nb = n >= 0 ? n : kFarRow;
         }
-        cur_p = -1; cur_g = kPaintNoSite; nxt_p = -1; nxt_g = 0;
-        {
-            const int s = cq_max(y0 - L, 0);
-            eblk = s >> 5;
-            ehw = c.h_ld(eblk) & (0xFFFFFFFFu << (s & 31));
-        }
-        c.seg_st(0, pack(0, kPaintNoSite));
+        start_cursor(y0);
+        c.seg_st(0, pack(cur_p < 0 ? 0 : cur_p - B0 * 32, cur_g));
         n0 = n1 = n2 = 0;
         for (int b = B0 - reach; b <= B0 + reach; ++b) q_add(b, 1);
         for (int B = B0; B * 32 < y1; ++B) {
