@@ -581,6 +581,67 @@ int chaqsdf_u8_device(const uint8_t* d_img, size_t w, size_t h, size_t stride, s
                                      d_workspace, workspace_bytes, stream);
 }
 
+// ---- multi-GPU exact path (variant E1: all-to-all between the passes) ---------------------------------------------
+size_t chaqsdf_col_part(size_t w, size_t nparts, size_t q, size_t* c0, size_t* c1) {
+    if (nparts == 0 || w == 0) return 0;
+    const size_t pw = align_up((w + nparts - 1) / nparts, 32);
+    const size_t a = q * pw < w ? q * pw : w, b = (q + 1) * pw < w ? (q + 1) * pw : w;
+    if (c0) *c0 = a;
+    if (c1) *c1 = b;
+    return pw;
+}
+
+int chaqsdf_rowscan_scatter_device(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
+                                   size_t row0, size_t nparts, void* const* d_parts, void* stream) {
+    if (!d_img || !d_parts) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (w == 0 || rows == 0) return fail(CHAQSDF_ERR_ARG, "empty image");
+    if (w > 32767) return fail(CHAQSDF_ERR_ARG, "exact fields need sides <= 32767");
+    if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
+    if (nparts == 0 || nparts > (size_t)kRowMaxParts) return fail(CHAQSDF_ERR_ARG, "1..16 column parts");
+    RowScanParams rp{};
+    rp.img = d_img; rp.inter = nullptr; rp.rows = (long long)rows; rp.w = (int)w;
+    rp.stride = (int)stride; rp.offset = (int)offset; rp.above = test_above ? 1 : 0; rp.cap = 0x7fff;
+    rp.nwords = (int)((w + 31) / 32);
+    rp.nparts = (int)nparts; rp.part_w = (int)chaqsdf_col_part(w, nparts, 0, nullptr, nullptr); rp.row0 = (long long)row0;
+    for (size_t q = 0; q < nparts; ++q) {
+        size_t c0 = 0, c1 = 0;
+        chaqsdf_col_part(w, nparts, q, &c0, &c1);
+        if (c1 > c0 && !d_parts[q]) return fail(CHAQSDF_ERR_ARG, "null part pointer");
+        rp.part[q] = (uint16_t*)d_parts[q];
+    }
+    const size_t smem = (size_t)kRowWarps * rp.nwords * sizeof(uint32_t);
+    const unsigned blocks = (unsigned)((rows + kRowWarps - 1) / kRowWarps);
+    rowscan_kernel<<<blocks, kRowWarps * 32, smem, (cudaStream_t)stream>>>(rp);
+    CQ_LAUNCHED("rowscan_kernel<scatter>", blocks, smem);
+    return CHAQSDF_OK;
+}
+
+int chaqsdf_fields_from_inter_device(const void* d_inter, size_t w, size_t h, size_t spread, int asymmetric,
+                                     int32_t* d_d2_in, int32_t* d_d2_out, float* d_f_in, float* d_f_out, float* d_sdf,
+                                     uint8_t* d_out, void* d_workspace, size_t workspace_bytes, void* stream) {
+    if (!d_inter) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (int rc = check_dims(w, h, spread)) return rc;
+    if (w > 32767 || h > 32767) return fail(CHAQSDF_ERR_ARG, "exact fields need sides <= 32767");
+    const int cap = 0x7fff;
+    EnvPlan pl;
+    if (int rc = plan_envelope(w, h, h, 1, cap, &pl)) return rc;
+    if (pl.ring_bytes > workspace_bytes || (pl.ring_bytes && !d_workspace)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
+    const Tables* tab;
+    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
+    EnvParams p{};
+    p.inter = (const uint16_t*)d_inter; p.w = (int)w; p.buf_rows = (int)h; p.out_begin = 0; p.out_end = (int)h;
+    p.band_rows = pl.band_rows; p.cap = cap; p.nw = pl.nw; p.table = tab->dq; p.out = d_out;
+    p.d2_in = d_d2_in; p.d2_out = d_d2_out; p.f_in = d_f_in; p.f_out = d_f_out; p.sdf = d_sdf;
+    p.gring = (uint32_t*)d_workspace;
+    return launch_env(pl, p, true, (cudaStream_t)stream);
+}
+size_t chaqsdf_fields_from_inter_workspace_bytes(size_t w, size_t h) {
+    if (check_dims(w, h, 1)) return 0;
+    EnvPlan pl;
+    if (plan_envelope(w, h, h, 1, 0x7fff, &pl)) return 0;
+    return pl.ring_bytes;
+}
+
 int chaqsdf_fields_device(const uint8_t* d_img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
                           size_t spread, int asymmetric, int32_t* d_d2_in, int32_t* d_d2_out, float* d_f_in,
                           float* d_f_out, float* d_sdf, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,

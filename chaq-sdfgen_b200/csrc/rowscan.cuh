@@ -23,6 +23,7 @@
 namespace chaq {
 
 constexpr int kRowWarps = 4;  // warps (= rows) per CTA
+constexpr int kRowMaxParts = 16;  // column parts of the scatter mode (one per GPU)
 constexpr int kFar = 1 << 20; // "no such pixel" position offset; larger than any cap, small enough not to overflow
 
 __device__ __forceinline__ uint32_t class_nibble(uint32_t wd, bool above) {
@@ -43,6 +44,12 @@ struct RowScanParams {
     int record;          // 0: [rows][w] uint16 with the class in bit 15; 1: records (below)
     int wp;              // record mode: w rounded up to 128
     long long rs_bytes;  // record mode: bytes per record = 2*wp + wp/8
+    // scatter mode (nparts > 0; the all-to-all of the multi-GPU exact path fused into the store): the row goes out in
+    // column parts of part_w columns (a multiple of 32; the last part takes what is left), part q to part[q], which
+    // holds ALL image rows of that part's columns: element (image row r, column x) at part[q][r * width(q) + x - q*part_w]
+    int nparts, part_w;
+    long long row0;      // image row of row 0 of this launch
+    uint16_t* part[kRowMaxParts];
 };
 
 __global__ void __launch_bounds__(kRowWarps * 32) rowscan_kernel(RowScanParams p) {
@@ -169,15 +176,23 @@ __global__ void __launch_bounds__(kRowWarps * 32) rowscan_kernel(RowScanParams p
                     y1 = c ? 1 : y1 + 1;
                 }
             }
-            if ((nvalid == 32 || rec) && vec_ok) {  // a record has room for the whole last word (padding: nothing in reach)
-                uint4* d4 = reinterpret_cast<uint4*>(dst + x0);
+            uint16_t* wdst = dst + x0;
+            bool v_ok = vec_ok;
+            if (p.nparts > 0) {  // this word belongs to one column part (parts start at multiples of 32 columns)
+                const int q = x0 / p.part_w;
+                const int pw = min(p.part_w, w - q * p.part_w);
+                wdst = p.part[q] + (size_t)(p.row0 + row) * (size_t)pw + (size_t)(x0 - q * p.part_w);
+                v_ok = (reinterpret_cast<uintptr_t>(wdst) & 15) == 0;
+            }
+            if ((nvalid == 32 || rec) && v_ok) {  // a record has room for the whole last word (padding: nothing in reach)
+                uint4* d4 = reinterpret_cast<uint4*>(wdst);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                     d4[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
             } else {
 #pragma unroll
                 for (int b = 0; b < 32; ++b)  // static indices keep packed[] in registers
-                    if (b < nvalid) dst[x0 + b] = (uint16_t)((b & 1) ? packed[b >> 1] >> 16 : packed[b >> 1] & 0xffffu);
+                    if (b < nvalid) wdst[b] = (uint16_t)((b & 1) ? packed[b >> 1] >> 16 : packed[b >> 1] & 0xffffu);
             }
         }
     }

@@ -32,7 +32,8 @@ SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
            "chaqsdf_inter_row_bytes",
            "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
-           "chaqsdf_fields_device"]
+           "chaqsdf_fields_device", "chaqsdf_col_part", "chaqsdf_rowscan_scatter_device",
+           "chaqsdf_fields_from_inter_workspace_bytes", "chaqsdf_fields_from_inter_device"]
 
 
 def lib():
@@ -71,6 +72,12 @@ def lib():
     L.chaqsdf_rowscan_device.argtypes = [vp, sz, sz, sz, sz, i, sz, vp, vp]
     L.chaqsdf_envelope_device.argtypes = [vp, sz, sz, sz, sz, sz, i, vp, vp, sz, vp]
     L.chaqsdf_fields_device.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp, vp, vp, vp, vp, vp, sz, vp]
+    L.chaqsdf_col_part.argtypes = [sz, sz, sz, C.POINTER(sz), C.POINTER(sz)]
+    L.chaqsdf_col_part.restype = sz
+    L.chaqsdf_rowscan_scatter_device.argtypes = [vp, sz, sz, sz, sz, i, sz, sz, C.POINTER(vp), vp]
+    L.chaqsdf_fields_from_inter_workspace_bytes.argtypes = [sz, sz]
+    L.chaqsdf_fields_from_inter_workspace_bytes.restype = sz
+    L.chaqsdf_fields_from_inter_device.argtypes = [vp, sz, sz, sz, i, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     _lib = L
     return L
 
@@ -376,3 +383,123 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
     if events:
         events[3].record()
     return out
+
+
+# ---------------------------------------------------------------- exact fields over several GPUs (all-to-all, variant E1)
+_FIELD_DT = None
+
+
+def col_part(w, nparts, q):
+    """Columns [c0, c1) of part q when a w-column image is cut into nparts column parts (chaqsdf_col_part)."""
+    c0, c1 = C.c_size_t(), C.c_size_t()
+    lib().chaqsdf_col_part(w, nparts, q, C.byref(c0), C.byref(c1))
+    return c0.value, c1.value
+
+
+def rowscan_scatter_device(d_img, w, rows, row0, part_ptrs, stride=1, offset=0, test_above=True, stream=None):
+    """Pass 1 of the exact path on `rows` rows starting at image row row0, stored by column part straight into the
+    buffers at part_ptrs (device addresses, one per part; peers' buffers when they are peer-mapped)."""
+    arr = (C.c_void_p * len(part_ptrs))(*part_ptrs)
+    _check(lib().chaqsdf_rowscan_scatter_device(_ptr(d_img), w, rows, stride, offset, int(test_above), row0, len(part_ptrs),
+                                                arr, _stream_ptr(stream)))
+
+
+def fields_from_inter_device(d_inter, w, h, spread=64, asymmetric=False, want=("d2_in", "d2_out", "out"), stream=None):
+    """Pass 2 of the exact path on a [h][w] uint16 intermediate (an image, or one column part of one)."""
+    import torch
+    dev = d_inter.device
+    dt = {"d2_in": torch.int32, "d2_out": torch.int32, "f_in": torch.float32, "f_out": torch.float32,
+          "sdf": torch.float32, "out": torch.uint8}
+    res = {k: torch.empty((h, w), dtype=dt[k], device=dev) for k in want}
+    ws = _workspace(int(lib().chaqsdf_fields_from_inter_workspace_bytes(w, h)), dev)
+    g = lambda k: _ptr(res.get(k))  # noqa: E731
+    _check(lib().chaqsdf_fields_from_inter_device(_ptr(d_inter), w, h, spread, int(asymmetric), g("d2_in"), g("d2_out"),
+                                                  g("f_in"), g("f_out"), g("sdf"), g("out"), _ptr(ws), ws.numel(),
+                                                  _stream_ptr(stream)))
+    return res
+
+
+def sdf_fields_a2a(d_band, w, h, spread=64, asymmetric=False, rank=0, world=1, group=None, state=None, stride=1, offset=0,
+                   test_above=True, want=("d2_in", "d2_out", "out"), events=None, mode=None):
+    """The exact (unwindowed) fields of one image over `world` ranks, one process per GPU: row bands for pass 1, an
+    all-to-all to column parts, pass 2 on whole columns (SURVEY.md 8(e) variant E1). d_band holds this rank's rows
+    (shard_rows); the result holds ALL rows of this rank's columns col_part(w, world, rank).
+    mode "store" (default on GPUs): pass 1 writes its rows straight into every rank's peer-mapped part buffer over
+    NVLink -- the all-to-all is the kernel's store -- then a pairwise device-side signal; mode "a2a": pass 1 into a
+    local buffer, packed blocks through torch.distributed (NCCL all_to_all_single; also the gloo-free fallback).
+    `state` (a dict) keeps the buffers and the peer mapping between calls; state["a2a"] says which mode runs."""
+    import torch
+    import torch.distributed as dist
+    dev = d_band.device
+    r0, r1 = shard_rows(h, world, rank)
+    rows = r1 - r0
+    c0, c1 = col_part(w, world, rank)
+    pw = c1 - c0
+    if state is None:
+        state = {}
+    key = ("a2a", w, h, rank, world)
+    if state.get("key") != key:
+        state.clear()
+        state["key"] = key
+        m = mode or os.environ.get("CHAQSDF_A2A") or ("store" if dev.type == "cuda" and world > 1 else "a2a")
+        maxpw = max(col_part(w, world, q)[1] - col_part(w, world, q)[0] for q in range(world))
+        if m == "store":
+            ok = 1
+            try:
+                import torch.distributed._symmetric_memory as symm
+                sym = symm.empty((2, h * maxpw), dtype=torch.int16, device=dev)
+                hdl = symm.rendezvous(sym, group if group is not None else dist.group.WORLD)
+                ptrs = [[hdl.get_buffer(q, (2, h * maxpw), torch.int16)[s].data_ptr() for q in range(world)] for s in range(2)]
+                state.update(sym=sym, hdl=hdl, ptrs=ptrs, step=0)
+            except Exception as e:  # noqa: BLE001 -- every rank falls back together
+                ok = 0
+                state["peer_error"] = repr(e)
+            flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            if not bool(flag.item()):
+                m = "a2a"
+        if m != "store":
+            state["part"] = torch.empty((h * maxpw,), dtype=torch.int16, device=dev)
+            state["local"] = torch.empty((rows, w), dtype=torch.int16, device=dev)
+        state["a2a"] = m
+    if events:
+        events[0].record()
+    if state["a2a"] == "store":
+        slot = state["step"] & 1
+        state["step"] += 1
+        rowscan_scatter_device(d_band, w, rows, r0, state["ptrs"][slot], stride=stride, offset=offset, test_above=test_above)
+        if events:
+            events[1].record()
+        hdl = state["hdl"]
+        for q in range(world):
+            if q != rank:
+                hdl.put_signal(q, slot, 20000)
+        for q in range(world):
+            if q != rank:
+                hdl.wait_signal(q, slot, 20000)
+        part = state["sym"][slot][:h * pw].view(h, pw)
+    else:
+        local = state["local"]
+        rowscan_scatter_device(d_band, w, rows, 0, [local.data_ptr()], stride=stride, offset=offset, test_above=test_above)
+        if events:
+            events[1].record()
+        part = state["part"][:h * pw].view(h, pw)
+        if world == 1:
+            part.copy_(local)
+        else:
+            send = [local[:, a:b].contiguous() for (a, b) in (col_part(w, world, q) for q in range(world))]
+            recv = []
+            for q in range(world):
+                q0, q1 = shard_rows(h, world, q)
+                recv.append(part[q0:q1])  # rows of rank q, my columns: contiguous in the part buffer
+            dist.all_to_all(recv, send, group=group)
+    if events:
+        events[2].record()
+    if pw == 0:  # more ranks than 32-column parts: nothing to do here
+        dtm = {"d2_in": torch.int32, "d2_out": torch.int32, "f_in": torch.float32, "f_out": torch.float32,
+               "sdf": torch.float32, "out": torch.uint8}
+        return {k: torch.empty((h, 0), dtype=dtm[k], device=dev) for k in want}
+    res = fields_from_inter_device(part, pw, h, spread=spread, asymmetric=asymmetric, want=want)
+    if events:
+        events[3].record()
+    return res

@@ -132,6 +132,23 @@ int chaqsdf_fields_device(const uint8_t* d_img, size_t w, size_t h, size_t strid
                           float* d_f_out, float* d_sdf, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
                           void* stream);
 
+/* ---- exact fields over several GPUs: all-to-all between the passes (SURVEY.md 8(e) variant E1) --------
+ * The unwindowed column pass needs whole columns, so the image is cut into row bands for pass 1 and into column
+ * parts for pass 2. chaqsdf_col_part gives part q of nparts: columns [*c0, *c1) (parts start at multiples of 32
+ * columns; returns the nominal part width). chaqsdf_rowscan_scatter_device runs pass 1 on `rows` rows starting at
+ * image row row0 and stores each row straight into the parts' buffers -- d_parts[q] is a device pointer (this
+ * device's or a peer-mapped one of another GPU: the all-to-all is the store) to a [h][c1-c0] uint16 buffer holding
+ * ALL image rows of that part. After every band has been stored (caller's barrier), each owner runs
+ * chaqsdf_fields_from_inter_device on its buffer as an image of width c1-c0: same outputs as chaqsdf_fields_device,
+ * for its columns. */
+size_t chaqsdf_col_part(size_t w, size_t nparts, size_t q, size_t* c0, size_t* c1);
+int chaqsdf_rowscan_scatter_device(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset,
+                                   int test_above, size_t row0, size_t nparts, void* const* d_parts, void* stream);
+size_t chaqsdf_fields_from_inter_workspace_bytes(size_t w, size_t h);
+int chaqsdf_fields_from_inter_device(const void* d_inter, size_t w, size_t h, size_t spread, int asymmetric,
+                                     int32_t* d_d2_in, int32_t* d_d2_out, float* d_f_in, float* d_f_out, float* d_sdf,
+                                     uint8_t* d_out, void* d_workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -665,3 +665,37 @@ def test_reference_main_runs_on_the_dropin(pkg, tmp_path):
     assert r.returncode == 0, r.stderr
     from oracle import Oracle
     assert np.array_equal(np.asarray(Image.open(dst)), Oracle().sdf(np.ascontiguousarray(rgba[..., 3]), 1500, 1500, spread=32))
+
+
+def test_exact_fields_by_column_parts(pkg, oracle):
+    """The pieces of the multi-GPU exact path (row bands -> all-to-all -> column parts, SURVEY.md 8(e) variant E1) on
+    one device: pass 1 of two row bands scattered into three column-part buffers (the store is the all-to-all), pass 2
+    per part as an image of the part's width; the parts side by side must be the oracle's exact fields."""
+    rng = np.random.default_rng(61)
+    for (h, w, nparts, bands) in ((300, 1000, 3, 2), (257, 96, 4, 3), (64, 2050, 8, 1), (1100, 700, 2, 5)):
+        img = random_shapes(rng, h, w)
+        d = torch.from_numpy(img).cuda()
+        parts = []
+        for q in range(nparts):
+            c0, c1 = pkg.col_part(w, nparts, q)
+            parts.append(torch.zeros((h, max(c1 - c0, 1)), dtype=torch.int16, device="cuda"))
+        for b in range(bands):
+            r0, r1 = pkg.shard_rows(h, bands, b)
+            pkg.rowscan_scatter_device(d[r0:r1], w, r1 - r0, r0, [p.data_ptr() for p in parts])
+        out, sdf, din, dout = oracle.sdf(img, w, h, spread=24, fields=True)
+        for q in range(nparts):
+            c0, c1 = pkg.col_part(w, nparts, q)
+            if c1 == c0:
+                continue
+            res = pkg.fields_from_inter_device(parts[q][:, :c1 - c0].contiguous() if parts[q].shape[1] != c1 - c0 else parts[q],
+                                               c1 - c0, h, spread=24, want=("d2_in", "d2_out", "out", "sdf"))
+            torch.cuda.synchronize()
+            assert np.array_equal(res["d2_in"].cpu().numpy(), din[:, c0:c1]), (h, w, q)
+            assert np.array_equal(res["d2_out"].cpu().numpy(), dout[:, c0:c1]), (h, w, q)
+            assert np.array_equal(res["out"].cpu().numpy(), out[:, c0:c1]), (h, w, q)
+            assert np.array_equal(res["sdf"].cpu().numpy().view(np.uint32), sdf[:, c0:c1].view(np.uint32)), (h, w, q)
+    # world 1 through the sharded entry (no process group needed)
+    img = random_shapes(rng, 500, 640)
+    res = pkg.sdf_fields_a2a(torch.from_numpy(img).cuda(), 640, 500, spread=24)
+    out, sdf, din, dout = oracle.sdf(img, 640, 500, spread=24, fields=True)
+    assert np.array_equal(res["d2_in"].cpu().numpy(), din) and np.array_equal(res["out"].cpu().numpy(), out)
