@@ -487,11 +487,12 @@ def sdf_fields_a2a(d_band, w, h, spread=64, asymmetric=False, rank=0, world=1, g
         if world == 1:
             part.copy_(local)
         else:
-            send = [local[:, a:b].contiguous() for (a, b) in (col_part(w, world, q) for q in range(world))]
+            # (as bytes: NCCL has no 16-bit integer type)
+            send = [local[:, a:b].contiguous().view(torch.uint8) for (a, b) in (col_part(w, world, q) for q in range(world))]
             recv = []
             for q in range(world):
                 q0, q1 = shard_rows(h, world, q)
-                recv.append(part[q0:q1])  # rows of rank q, my columns: contiguous in the part buffer
+                recv.append(part[q0:q1].view(torch.uint8))  # rows of rank q, my columns: contiguous in the part buffer
             dist.all_to_all(recv, send, group=group)
     if events:
         events[2].record()
