@@ -204,22 +204,33 @@ struct HullPaint {
     CQ_HD void paint(int Y, int r0, int r1, uint32_t T) {
         int k = 0;
         uint32_t e = c.seg_ld(0);
-        int cr = (int)(e >> 16) - kPaintRelBias, cg = (int)(e & 0xFFFFu);
+        int cg = (int)(e & 0xFFFFu);
         int ch = cg * cg;
+        int d = (r0 - Y) - ((int)(e >> 16) - kPaintRelBias);  // row - owner's row
+        uint32_t t = T >> (r0 - Y);                           // bit 0: a new owner starts at this row
+        int nbd = nb - r0;                                    // rows until the class changes
+        const int lp1 = L + 1;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 4
+#endif
         for (int y = r0; y < r1; ++y) {
-            const int j = y - Y;
-            if ((T >> j) & 1u) {
+            if (t & 1u) {
                 e = c.seg_ld(++k);
-                cr = (int)(e >> 16) - kPaintRelBias;
                 cg = (int)(e & 0xFFFFu);
                 ch = cg * cg;
+                d = (y - Y) - ((int)(e >> 16) - kPaintRelBias);
             }
             ++upd;
-            if (CQ_UNLIKELY(y == nb)) class_flip(y);
-            const int d = j - cr;
+            if (CQ_UNLIKELY(nbd == 0)) {
+                class_flip(y);
+                nbd = nb - y;
+            }
             const int fc = d * d + ch;
-            const int v = cq_min(cq_min(upd, nb - y), L + 1);
+            const int v = cq_min(cq_min(upd, nbd), lp1);
             c.out(ecls, cq_min(fc, v * v));
+            ++d;
+            --nbd;
+            t >>= 1;
         }
     }
 
