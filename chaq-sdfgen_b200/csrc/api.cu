@@ -378,7 +378,8 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     // paint runs: starting one is cheap (the cursor is found by a local search), so short runs -- more CTAs than the
     // build, evening out dense and empty areas -- win: ~8 blocks at 16384^2
     const long long target_e = (long long)di.sms * 56;
-    long long eb = (strips * nbo + target_e - 1) / target_e;
+    const long long strips_e = (long long)n_img * p.nstrips_e;
+    long long eb = (strips_e * nbo + target_e - 1) / target_e;
     eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
     if (g_tuning.hull_eb > 0) eb = g_tuning.hull_eb;
     if (eb < 1) eb = 1;

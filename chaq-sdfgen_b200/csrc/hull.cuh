@@ -4,7 +4,7 @@
 // transform_float_sub (sdfgen.c:98-106) and transform_float_to_byte (sdfgen.c:75-96) as an exact integer
 // threshold look-up (tables.h).
 //
-//   hull_build_kernel  CTA = 4 warps = one 128-column strip x one run of <= 512 rows; lane = column. g8 rows
+//   hull_build_kernel  CTA = kHullWarps (2) warps = one strip of 32-column groups x one run of <= 512 rows; lane = column. g8 rows
 //                      arrive by cp.async (16-byte copies, one 32-row block per group, one block ahead); the
 //                      run's hull words live in shared memory until the run is done, then go out as 128-byte
 //                      lines. No context rows: a run only pushes its own rows. Also leaves one flag per
@@ -23,7 +23,10 @@
 
 namespace chaq {
 
-constexpr int kHullWarps = 4;
+#ifndef CQ_HULL_WARPS
+#define CQ_HULL_WARPS 2
+#endif
+constexpr int kHullWarps = CQ_HULL_WARPS;  // column groups (warps) per build CTA
 
 // Row distances in pass 1's record: one byte (spread <= 256) or, WIDE, one uint16 (spread <= 1024). Same kernels.
 template <bool WIDE> struct GVal { typedef uint8_t T; };
