@@ -119,7 +119,7 @@ bool pipeline_shape(size_t w, size_t h, size_t stride, size_t spread, size_t* ba
     if (chaq::tuning().pipe_rows > 0) band = (size_t)chaq::tuning().pipe_rows;
     band = (band + 31) & ~(size_t)31;
     if (band < 2 * spread + 64) band = (2 * spread + 64 + 31) & ~(size_t)31;
-    size_t first = ((size_t)16 << 20) / (w * stride);  // ~16 MB first/last band
+    size_t first = ((size_t)4 << 20) / (w * stride);   // ~4 MB first/last band (ramps up by doubling)
     if (chaq::tuning().pipe_first > 0) first = (size_t)chaq::tuning().pipe_first;
     first = (first + 31) & ~(size_t)31;
     if (first < spread + 32) first = (spread + 32 + 31) & ~(size_t)31;
