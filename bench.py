@@ -333,8 +333,6 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         sampler.start()
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3 if world == 1 else 4)] for _ in range(K)]
-    if world == 1:
-        pkg.profile_enable(True)  # the library's own CUDA events around the kernels of pass 2, on this stream
     l0 = pkg.launch_count()
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -346,7 +344,14 @@ def run_ours(args, rank, world, local_rank):
     launches = pkg.launch_count() - l0
     kernel_ms = None
     if world == 1:
-        kernel_ms = pkg.profile_mean_ms()  # mean over the timed steps (first 64)
+        # per-kernel times: a separate pass after the timed region, with the library's own CUDA events around each
+        # launch. Profiling runs pass 2 as ONE column part, kernels back to back; the timed step above overlaps 8
+        # column parts on streams, so its pass 2 is shorter than the sum of these.
+        pkg.profile_enable(True)
+        for _ in range(min(K, 20)):
+            step()
+        torch.cuda.synchronize()
+        kernel_ms = pkg.profile_mean_ms()
         pkg.profile_enable(False)
     clocks = sampler.stop() if rank == 0 else None
     ms_total = t_start.elapsed_time(t_end)
@@ -431,7 +436,9 @@ def run_ours(args, rank, world, local_rank):
         passes = {k: {"ms": ms_of[k], "GB/s": bytes_of[k] / (ms_of[k] * 1e-3) / 1e9 if bytes_of[k] else None,
                       "frac": bytes_of[k] / (ms_of[k] * 1e-3) / 1e9 / peak if bytes_of[k] else None,
                       "algorithmic_bytes": bytes_of[k]} for k in ms_of}
-        passes["pass2_total"] = {"ms": p2, "note": "build + junction merge (2 launches) + paint, CUDA events around the C-ABI call"}
+        passes["pass2_total"] = {"ms": p2, "note": "pass 2 as timed in the step (CUDA events around the C-ABI call): build + junction "
+                                 "rounds + paint of 8 column parts overlapping on streams; the per-kernel rows above are from a "
+                                 "separate profiled pass that runs them back to back as one part"}
         dom = max((k for k in ms_of if bytes_of[k]), key=lambda k: ms_of[k])  # the longest kernel of the step
         default_cfg = SIDE == 16384 and SPREAD == 256
         roofline = {"bound": "hbm", "kernel": dom + " (the longest kernel of the step)",

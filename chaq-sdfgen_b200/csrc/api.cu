@@ -58,6 +58,7 @@ Tuning read_tuning() {
     t.hull_sub = num("CHAQSDF_HULL_SUB");
     t.hull_eb = num("CHAQSDF_HULL_EB");
     t.hull_seq = getenv("CHAQSDF_HULL_SEQ") != nullptr;
+    t.hull_parts = num("CHAQSDF_HULL_PARTS");
     t.row8_wide = getenv("CHAQSDF_ROW8_WIDE") != nullptr;
     t.pipe_rows = num("CHAQSDF_PIPE_ROWS");
     t.pipe_first = num("CHAQSDF_PIPE_FIRST");
@@ -334,6 +335,40 @@ void prof_mark(int i, cudaStream_t st) {
     if (i == 3) ++g_prof_n;
 }
 
+// helper streams for the column parts of one pass-2 call (per device, created on first use, never destroyed)
+constexpr int kMaxParts = 16;
+struct PartStreams {
+    std::mutex mu;  // held while one call enqueues its parts (the enqueue is short; the work itself overlaps)
+    cudaStream_t s[kMaxParts - 1] = {};
+    cudaEvent_t fork = nullptr, join[kMaxParts - 1] = {};
+};
+std::map<int, PartStreams*> g_part_streams;
+int part_streams(PartStreams** out) {
+    int dev = 0;
+    CQ_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_mu);
+    PartStreams*& ps = g_part_streams[dev];
+    if (!ps) {
+        PartStreams* n = new PartStreams();
+        CQ_CUDA(cudaEventCreateWithFlags(&n->fork, cudaEventDisableTiming));
+        for (int i = 0; i < kMaxParts - 1; ++i) {
+            CQ_CUDA(cudaStreamCreateWithFlags(&n->s[i], cudaStreamNonBlocking));
+            CQ_CUDA(cudaEventCreateWithFlags(&n->join[i], cudaEventDisableTiming));
+        }
+        ps = n;
+    }
+    *out = ps;
+    return CHAQSDF_OK;
+}
+#define CQ_CUDA_UNLOCK(expr, ps)                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (expr);                                                                        \
+        if (e_ != cudaSuccess) {                                                                        \
+            (ps)->mu.unlock();                                                                          \
+            return fail(CHAQSDF_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));          \
+        }                                                                                               \
+    } while (0)
+
 // banded pass 2 as build / merge / paint (hull.cuh, paint.cuh)
 template <bool WIDE>
 int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
@@ -352,6 +387,7 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     p.ncg = (int)((w + 31) / 32); p.wc = p.ncg * 32;
     p.nstrips = (p.ncg + kHullWarps - 1) / kHullWarps; p.n_img = (int)n_img;
     p.nstrips_e = (p.ncg + kEmitWarps - 1) / kEmitWarps;
+    p.cg0 = 0; p.cg1 = p.ncg;
     p.out_begin = (int)out_begin; p.out_end = (int)out_end;
     p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2;
     // run lengths: enough CTAs to fill the machine a few times over, runs no longer than 512 rows (build) / 1024 (emit)
@@ -392,36 +428,72 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
         CQ_CUDA(cudaFuncSetAttribute(hull_build_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
         CQ_CUDA(cudaFuncSetAttribute(hull_build4_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
     }
-    prof_mark(0, st);
-    if (p.nsub == 4) hull_build4_kernel<WIDE><<<(unsigned)gb, kHullWarps * 32 * 4, smem_b, st>>>(p);
-    else hull_build_kernel<WIDE><<<(unsigned)gb, kHullWarps * 32, smem_b, st>>>(p);
-    CQ_LAUNCHED(p.nsub == 4 ? "hull_build4_kernel" : "hull_build_kernel", gb, smem_b);
-    prof_mark(1, st);
-    if (p.nruns_b > 1 && !g_tuning.hull_seq) {
-        const int njun = p.nruns_b - 1;
-        int nphase = hull_merge_phases(p.L, p.pb);
-        nphase = nphase < 1 ? 1 : (nphase > njun ? njun : nphase);
-        p.merge_nphase = nphase;
-        for (int phase = 0; phase < nphase; ++phase) {
-            const int nmine = (njun - phase + nphase - 1) / nphase;
-            if (nmine <= 0) continue;
-            p.merge_phase = phase;
-            const long long thr = (long long)n_img * nmine * p.w;
-            const unsigned gm = (unsigned)((thr + 255) / 256);
-            hull_merge_par_kernel<WIDE><<<gm, 256, 0, st>>>(p);
-            CQ_LAUNCHED("hull_merge_par_kernel", gm, 0);
-        }
-    } else if (p.nruns_b > 1) {
-        const long long cols = (long long)n_img * p.w;
-        const unsigned gm = (unsigned)((cols + 255) / 256);
-        hull_merge_kernel<WIDE><<<gm, 256, 0, st>>>(p);
-        CQ_LAUNCHED("hull_merge_kernel", gm, 0);
+    // Column parts on separate streams: the chains build -> junction rounds -> paint of different parts overlap, so
+    // the tail of one part's build (SMs idle while the last heavy CTAs finish) and its latency-bound junction rounds
+    // are filled with other parts' work. One part when the grid is small, when profiling per kernel, or when asked.
+    int nparts = 1;
+    if (n_img == 1 && !g_prof_on && p.nblk >= 4) nparts = p.ncg >= 256 ? 8 : (p.ncg >= 64 ? 4 : 1);
+    if (g_tuning.hull_parts > 0) nparts = (int)g_tuning.hull_parts;
+    if (nparts > kMaxParts) nparts = kMaxParts;
+    if (nparts > p.ncg / 4) nparts = p.ncg / 4 > 0 ? p.ncg / 4 : 1;
+    if (n_img != 1 || g_prof_on) nparts = 1;
+    PartStreams* ps = nullptr;
+    if (nparts > 1) {
+        if (int rc = part_streams(&ps)) return rc;
+        ps->mu.lock();
+        CQ_CUDA_UNLOCK(cudaEventRecord(ps->fork, st), ps);
     }
-    prof_mark(2, st);
-    hull_paint_kernel<WIDE><<<(unsigned)ge, kEmitWarps * 32, smem_e, st>>>(p);
-    CQ_LAUNCHED("hull_paint_kernel", ge, smem_e);
-    prof_mark(3, st);
-    return CHAQSDF_OK;
+    const int per = ((p.ncg + nparts - 1) / nparts + 3) & ~3;  // parts start at multiples of 4 column groups
+    int rc_all = CHAQSDF_OK;
+    for (int k = 0; k < nparts && rc_all == CHAQSDF_OK; ++k) {
+        HullParams q = p;
+        q.cg0 = k * per; q.cg1 = q.cg0 + per < p.ncg ? q.cg0 + per : p.ncg;
+        if (q.cg0 >= q.cg1) break;
+        cudaStream_t sk = k == 0 ? st : ps->s[k - 1];
+        if (k > 0) CQ_CUDA_UNLOCK(cudaStreamWaitEvent(sk, ps->fork, 0), ps);
+        q.nstrips = (q.cg1 - q.cg0 + kHullWarps - 1) / kHullWarps;
+        q.nstrips_e = (q.cg1 - q.cg0 + kEmitWarps - 1) / kEmitWarps;
+        const long long gbk = (long long)n_img * q.nstrips * q.nruns_b, gek = (long long)n_img * q.nstrips_e * q.nruns_e;
+        const long long wpart = (long long)(q.cg1 * 32 < q.w ? q.cg1 * 32 : q.w) - q.cg0 * 32;
+        rc_all = [&]() -> int {
+            if (k == 0) prof_mark(0, st);
+            if (q.nsub == 4) hull_build4_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32 * 4, smem_b, sk>>>(q);
+            else hull_build_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32, smem_b, sk>>>(q);
+            CQ_LAUNCHED(q.nsub == 4 ? "hull_build4_kernel" : "hull_build_kernel", gbk, smem_b);
+            if (k == 0) prof_mark(1, st);
+            if (q.nruns_b > 1 && !g_tuning.hull_seq) {
+                const int njun = q.nruns_b - 1;
+                int nphase = hull_merge_phases(q.L, q.pb);
+                nphase = nphase < 1 ? 1 : (nphase > njun ? njun : nphase);
+                q.merge_nphase = nphase;
+                for (int phase = 0; phase < nphase; ++phase) {
+                    const int nmine = (njun - phase + nphase - 1) / nphase;
+                    if (nmine <= 0) continue;
+                    q.merge_phase = phase;
+                    const long long thr = (long long)n_img * nmine * wpart;
+                    const unsigned gm = (unsigned)((thr + 255) / 256);
+                    hull_merge_par_kernel<WIDE><<<gm, 256, 0, sk>>>(q);
+                    CQ_LAUNCHED("hull_merge_par_kernel", gm, 0);
+                }
+            } else if (q.nruns_b > 1) {
+                const long long cols = (long long)n_img * wpart;
+                const unsigned gm = (unsigned)((cols + 255) / 256);
+                hull_merge_kernel<WIDE><<<gm, 256, 0, sk>>>(q);
+                CQ_LAUNCHED("hull_merge_kernel", gm, 0);
+            }
+            if (k == 0) prof_mark(2, st);
+            hull_paint_kernel<WIDE><<<(unsigned)gek, kEmitWarps * 32, smem_e, sk>>>(q);
+            CQ_LAUNCHED("hull_paint_kernel", gek, smem_e);
+            if (k == 0) prof_mark(3, st);
+            return CHAQSDF_OK;
+        }();
+        if (rc_all == CHAQSDF_OK && k > 0) {
+            if (cudaEventRecord(ps->join[k - 1], sk) != cudaSuccess || cudaStreamWaitEvent(st, ps->join[k - 1], 0) != cudaSuccess)
+                rc_all = fail(CHAQSDF_ERR_CUDA, "joining the column parts failed");
+        }
+    }
+    if (ps) ps->mu.unlock();
+    return rc_all;
 }
 
 int launch_hull(size_t spread, const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,

@@ -52,6 +52,8 @@ struct HullParams {
     int wp, w, buf_rows, nblk;
     int wc;                  // ncg * 32
     int ncg, nstrips, n_img;
+    int cg0, cg1;            // column groups [cg0, cg1) of this launch (the image may be cut into column parts that
+                             // run on different streams); nstrips / nstrips_e count the strips of this range
     int nstrips_e;           // strips of kEmitWarps column groups (emit kernel)
     int out_begin, out_end;
     int pb;                  // blocks per build run
@@ -171,10 +173,10 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
     const int run = (int)(id % p.nruns_b); id /= p.nruns_b;
     const int strip = (int)(id % p.nstrips);
     const int img = (int)(id / p.nstrips);
-    const int cg = strip * kHullWarps + cgi;
+    const int cg = p.cg0 + strip * kHullWarps + cgi;
     const int b0 = run * p.pb, b1 = b0 + p.pb < p.nblk ? b0 + p.pb : p.nblk;
     const int s0 = b0 + sub * p.sb, s1 = s0 + p.sb < b1 ? s0 + p.sb : b1;
-    const bool active = cg < p.ncg;
+    const bool active = cg < p.cg1;
     if (NSUB == 1 && !active) return;  // no barrier below in this shape
     uint32_t* gbits = reinterpret_cast<uint32_t*>(s_hull + (size_t)cgi * p.pb * 128) + lane;
     const uint8_t* recbase = p.inter + (long long)img * p.buf_rows * p.rs;
@@ -233,8 +235,9 @@ template <bool WIDE>
 __global__ void __launch_bounds__(256) hull_merge_kernel(HullParams p) {
     constexpr int kG = (int)sizeof(typename GVal<WIDE>::T);
     const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (t >= (long long)p.n_img * p.w) return;
-    const int img = (int)(t / p.w), x = (int)(t - (long long)img * p.w);
+    const int x0 = p.cg0 * 32, wpart = min(p.cg1 * 32, p.w) - x0;
+    if (t >= (long long)p.n_img * wpart) return;
+    const int img = (int)(t / wpart), x = x0 + (int)(t - (long long)img * wpart);
     HullMergeCtx<WIDE> c;
     c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
     c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x * kG;
@@ -253,11 +256,12 @@ __global__ void __launch_bounds__(256) hull_merge_par_kernel(HullParams p) {
     const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
     const int njun = p.nruns_b - 1;                       // junctions 1 .. njun (junction k is at block k*pb)
     const int nmine = (njun - p.merge_phase + p.merge_nphase - 1) / p.merge_nphase;  // k = 1 + phase + i*nphase
-    const long long per_img = (long long)nmine * p.w;
+    const int x0 = p.cg0 * 32, wpart = min(p.cg1 * 32, p.w) - x0;
+    const long long per_img = (long long)nmine * wpart;
     if (t >= per_img * p.n_img) return;
     const int img = (int)(t / per_img);
     const long long r = t - (long long)img * per_img;
-    const int k = 1 + p.merge_phase + p.merge_nphase * (int)(r / p.w), x = (int)(r % p.w);
+    const int k = 1 + p.merge_phase + p.merge_nphase * (int)(r / wpart), x = x0 + (int)(r % wpart);
     HullMergeCtx<WIDE> c;
     c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
     c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x * kG;

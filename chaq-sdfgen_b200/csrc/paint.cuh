@@ -125,8 +125,8 @@ __global__ void __launch_bounds__(kEmitWarps * 32, 8) hull_paint_kernel(HullPara
     const int run = (int)(id % p.nruns_e); id /= p.nruns_e;
     const int strip = (int)(id % p.nstrips_e);
     const int img = (int)(id / p.nstrips_e);
-    const int cg = strip * kEmitWarps + warp;
-    if (cg >= p.ncg) return;
+    const int cg = p.cg0 + strip * kEmitWarps + warp;
+    if (cg >= p.cg1) return;
     // runs are cut at multiples of 32 buffer rows so that whole blocks can be written at once
     const int bfirst = p.out_begin >> 5;
     int y0 = (bfirst + run * p.eb) * 32, y1 = y0 + p.eb * 32;

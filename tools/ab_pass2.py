@@ -30,19 +30,23 @@ for i in range(2):
     pkg.rowscan_device(d, side, side, spread, inter)
     pkg.envelope_device(inter, side, side, 0, side, spread, False, out, workspace=ws)
 torch.cuda.synchronize()
-pkg.profile_enable(True)
 ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(iters)]
-for i in range(iters):
+for i in range(iters):  # the step as it runs in production (column parts of pass 2 overlap on streams)
     ev[i][0].record()
     pkg.rowscan_device(d, side, side, spread, inter)
     ev[i][1].record()
     pkg.envelope_device(inter, side, side, 0, side, spread, False, out, workspace=ws)
     ev[i][2].record()
 torch.cuda.synchronize()
+pkg.profile_enable(True)  # per-kernel times: one part, kernels back to back
+for i in range(iters):
+    pkg.rowscan_device(d, side, side, spread, inter)
+    pkg.envelope_device(inter, side, side, 0, side, spread, False, out, workspace=ws)
+torch.cuda.synchronize()
 ms = pkg.profile_mean_ms()
 pkg.profile_enable(False)
 p1 = min(e[0].elapsed_time(e[1]) for e in ev)
 p2 = min(e[1].elapsed_time(e[2]) for e in ev)
 crc = zlib.crc32(out.cpu().numpy().tobytes())
-print(f"{kind} {side}^2 s{spread} env[{os.environ.get('CHAQSDF_EMIT','')},{os.environ.get('CHAQSDF_BUILD','')}]: "
+print(f"{kind} {side}^2 s{spread} parts[{os.environ.get('CHAQSDF_HULL_PARTS','auto')}]: "
       f"pass1 {p1:.3f} pass2 {p2:.3f} ms  kernels {ms}  crc {crc:08x}")
