@@ -1,5 +1,6 @@
 """Device-timed runs of the other BASELINE configs on one GPU (parity cases, not bench lines):
-   python tools/time_configs.py [c2] [c3] [c5]      c2: 4096^2 s64   c3: 4096 glyphs 256^2 s16   c5: 32768^2 s1024"""
+   python tools/time_configs.py [c2] [c3] [c4] [c5]   c2: 4096^2 s64   c3: 4096 glyphs 256^2 s16   c4: 16384^2 s256 (one
+   call for both passes, unlike bench.py's two)   c5: 32768^2 s1024"""
 import json
 import os
 import sys
@@ -30,8 +31,8 @@ def timed(fn, iters=5):
 
 
 for c in which:
-    if c == "c2":
-        n, spread = 4096, 64
+    if c in ("c2", "c4"):
+        n, spread = (4096, 64) if c == "c2" else (16384, 256)
         d = torch.from_numpy(bench.syn_discs(n)).cuda()
         out = torch.empty((n, n), dtype=torch.uint8, device="cuda")
         ws = torch.empty(pkg.workspace_bytes(n, n, spread), dtype=torch.uint8, device="cuda")
