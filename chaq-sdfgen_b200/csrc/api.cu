@@ -18,6 +18,7 @@
 #include "rowscan8.cuh"
 #include "hull.cuh"
 #include "paint.cuh"
+#include "paint2.cuh"
 #include "glyph.cuh"
 #include "tuning.h"
 
@@ -63,6 +64,7 @@ Tuning read_tuning() {
     t.pipe_rows = num("CHAQSDF_PIPE_ROWS");
     t.pipe_first = num("CHAQSDF_PIPE_FIRST");
     if (const char* m = getenv("CHAQSDF_DT2D")) t.dt2d_mode = m[0] == 's' ? 1 : (m[0] == 'e' ? 2 : 0);
+    if (const char* m = getenv("CHAQSDF_PAINT")) t.paint = m[0] == 'l' ? 1 : (m[0] == 'b' ? 3 : 0);  // "level": the level-tracking kernel; "bucket": never the direct table
     if (const char* m = getenv("CHAQSDF_GLYPH")) t.glyph = m[0] == '0' || m[0] == 'n' ? 1 : 2;
     return t;
 }
@@ -79,6 +81,10 @@ struct Tables {
     LevelTable* dl = nullptr;
     LevelTable hl;              // host copy (cap_eff decides the geometry of the banded path)
     uint8_t* dlut = nullptr;    // cap_eff <= kGlyphMaxC: byte for (class, clamped D2), for the fused small-image kernel
+    uint8_t* dlutb = nullptr;   // cap_eff <= 256: the same table at its own stride, for the banded paint kernel
+    int lutb_stride = 0;        // bytes per class (c2 + 1 rounded up to 16)
+    uint8_t* dlutk = nullptr;   // bucketed form: per class nbk 32-bit step masks, then nbk first bytes (paint.cuh)
+    int lutk_stride = 0, lutk_nbk = 0;
 };
 std::map<std::tuple<int, size_t, int>, Tables> g_tables;
 
@@ -124,6 +130,44 @@ int get_table(size_t spread, int asymmetric, const Tables** out) {
             CQ_CUDA(cudaMalloc(&t.dlut, lut.size()));
             CQ_CUDA(cudaMemcpy(t.dlut, lut.data(), lut.size(), cudaMemcpyHostToDevice));
         }
+        if (t.hl.cap_eff <= 256) {
+            t.lutb_stride = (int)align_up((size_t)t.hl.c2 + 1, 16);
+            std::string lut((size_t)2 * t.lutb_stride, '\0');
+            for (int cls = 0; cls < 2; ++cls) {
+                int m = 0;  // thresholds rise with the level: walk them once
+                for (int d2 = 0; d2 <= t.hl.c2; ++d2) {
+                    while (m < 255 && t.hl.thr[cls][m + 1] <= d2) ++m;
+                    lut[(size_t)cls * t.lutb_stride + d2] = (char)(uint8_t)(cls ? m : 255 - m);
+                }
+            }
+            CQ_CUDA(cudaMalloc(&t.dlutb, lut.size()));
+            CQ_CUDA(cudaMemcpy(t.dlutb, lut.data(), lut.size(), cudaMemcpyHostToDevice));
+            // bucketed form, possible when the byte never moves by more than one step (inside up, outside down):
+            // per class nbk entries of {32-bit step mask, first byte} (paint2.cuh)
+            const int nbk = (t.hl.c2 >> 5) + 1;
+            const int kstride = (int)align_up((size_t)nbk * 8, 16);
+            std::string kb((size_t)2 * kstride, '\0');
+            bool ok = true;
+            for (int cls = 0; cls < 2 && ok; ++cls) {
+                const uint8_t* bytes = (const uint8_t*)lut.data() + (size_t)cls * t.lutb_stride;
+                uint32_t* ent = (uint32_t*)(&kb[(size_t)cls * kstride]);
+                for (int i = 0; i < nbk; ++i) {
+                    uint32_t m = 0;
+                    for (int j = 1; j < 32 && i * 32 + j <= t.hl.c2; ++j) {
+                        const int d = (int)bytes[i * 32 + j] - (int)bytes[i * 32 + j - 1];
+                        if (d == (cls ? 1 : -1)) m |= 1u << j;
+                        else if (d != 0) ok = false;
+                    }
+                    ent[2 * i] = m;
+                    ent[2 * i + 1] = bytes[i * 32];
+                }
+            }
+            if (ok) {
+                t.lutk_stride = kstride; t.lutk_nbk = nbk;
+                CQ_CUDA(cudaMalloc(&t.dlutk, kb.size()));
+                CQ_CUDA(cudaMemcpy(t.dlutk, kb.data(), kb.size(), cudaMemcpyHostToDevice));
+            }
+        }
         it = g_tables.emplace(key, t).first;
     }
     *out = &it->second;
@@ -157,13 +201,14 @@ size_t banded_rs(size_t w, size_t spread) {
 }
 // scratch of the banded pass 2 (hull.cuh, paint.cuh): hull bitmask + transposed class bits (one word per
 // (32-row block, column) each) + one flag byte per (block, 32-column group)
+constexpr size_t kWorkBytes = 256;  // work-item counters of the persistent paint kernels (one per column part)
 size_t hull_words_bytes(size_t n_img, size_t w, size_t buf_rows) {
     const size_t ncg = (w + 31) / 32, nblk = (buf_rows + 31) / 32;
     return align_up(n_img * nblk * ncg * 32 * sizeof(uint32_t), 256);
 }
 size_t hull_ws_bytes(size_t n_img, size_t w, size_t buf_rows) {
     const size_t nblk = (buf_rows + 31) / 32, ncg = (w + 31) / 32;
-    return 2 * hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256);
+    return 2 * hull_words_bytes(n_img, w, buf_rows) + align_up(n_img * nblk * ncg, 256) + kWorkBytes;
 }
 size_t inter_row_bytes(size_t w, size_t spread) { return banded(spread) ? banded_rs(w, spread) : w * sizeof(uint16_t); }
 
@@ -381,6 +426,15 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     p.hull = (uint32_t*)d_ws;
     p.clsT = (uint32_t*)((uint8_t*)d_ws + hull_words_bytes(n_img, w, buf_rows));
     p.flags = (uint8_t*)d_ws + 2 * hull_words_bytes(n_img, w, buf_rows);
+    unsigned* const work0 = (unsigned*)((uint8_t*)d_ws + hull_ws_bytes(n_img, w, buf_rows) - kWorkBytes);
+    // staged paint kernel: the direct table when it fits beside the warps' staging, else the bucketed one
+    const bool lut_direct = !WIDE && tab->dlutb && hull_paint2_smem(2 * tab->lutb_stride) <= (size_t)di.max_smem_optin &&
+                            g_tuning.paint != 3;
+    const bool lut_bucket = !WIDE && !lut_direct && tab->dlutk && hull_paint2_smem(2 * tab->lutk_stride) <= (size_t)di.max_smem_optin;
+    const bool use_lut = (lut_direct || lut_bucket) && g_tuning.paint != 1;
+    p.lut = lut_direct ? tab->dlutb : tab->dlutk; p.lut_stride = lut_direct ? tab->lutb_stride : tab->lutk_stride;
+    p.lut_nbk = lut_direct ? 0 : tab->lutk_nbk; p.work = nullptr;
+    if (!use_lut) p.lut = nullptr;
     p.wp = banded_wp(w); p.w = (int)w; p.buf_rows = (int)buf_rows;
     p.rs = (long long)banded_rs(w, WIDE ? 1024 : 256); p.cls_off = WIDE ? 2 * p.wp : p.wp;
     p.nblk = (int)((buf_rows + 31) / 32);
@@ -417,6 +471,10 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     const long long strips_e = (long long)n_img * p.nstrips_e;
     long long eb = (strips_e * nbo + target_e - 1) / target_e;
     eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
+    if (use_lut) {  // persistent kernel, one item per (column group, run): ~6 items per resident warp
+        eb = ((long long)n_img * p.ncg * nbo) / ((long long)di.sms * kP2Warps * 6);
+        eb = eb < 4 ? 4 : (eb > 32 ? 32 : eb);
+    }
     if (g_tuning.hull_eb > 0) eb = g_tuning.hull_eb;
     if (eb < 1) eb = 1;
     if (eb > nbo) eb = nbo;
@@ -424,6 +482,11 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     const long long gb = strips * p.nruns_b, ge = (long long)n_img * p.nstrips_e * p.nruns_e;
     if (gb > 0x7fffffffLL || ge > 0x7fffffffLL) return fail(CHAQSDF_ERR_ARG, "too many runs for one grid");
     const size_t smem_b = hull_build_smem(p.pb, p.nsub, WIDE), smem_e = hull_paint_smem();
+    const size_t smem_l = use_lut ? hull_paint2_smem(2 * p.lut_stride) : 0;
+    if (use_lut) {
+        if (lut_direct) CQ_CUDA(cudaFuncSetAttribute(hull_paint2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l));
+        else CQ_CUDA(cudaFuncSetAttribute(hull_paint2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_l));
+    }
     if (smem_b > 48 * 1024) {
         CQ_CUDA(cudaFuncSetAttribute(hull_build_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
         CQ_CUDA(cudaFuncSetAttribute(hull_build4_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
@@ -449,6 +512,7 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
         HullParams q = p;
         q.cg0 = k * per; q.cg1 = q.cg0 + per < p.ncg ? q.cg0 + per : p.ncg;
         if (q.cg0 >= q.cg1) break;
+        q.work = use_lut ? work0 + k : nullptr;
         cudaStream_t sk = k == 0 ? st : ps->s[k - 1];
         if (k > 0) CQ_CUDA_UNLOCK(cudaStreamWaitEvent(sk, ps->fork, 0), ps);
         q.nstrips = (q.cg1 - q.cg0 + kHullWarps - 1) / kHullWarps;
@@ -482,8 +546,18 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
                 CQ_LAUNCHED("hull_merge_kernel", gm, 0);
             }
             if (k == 0) prof_mark(2, st);
-            hull_paint_kernel<WIDE><<<(unsigned)gek, kEmitWarps * 32, smem_e, sk>>>(q);
-            CQ_LAUNCHED("hull_paint_kernel", gek, smem_e);
+            if (use_lut) {
+                const long long items = (long long)n_img * (q.cg1 - q.cg0) * q.nruns_e;
+                long long gl = (items + kP2Warps - 1) / kP2Warps;
+                const long long cap = (di.sms + nparts - 1) / nparts;
+                gl = gl > cap ? cap : gl;
+                if (lut_direct) hull_paint2_kernel<true><<<(unsigned)gl, kP2Warps * 32, smem_l, sk>>>(q);
+                else hull_paint2_kernel<false><<<(unsigned)gl, kP2Warps * 32, smem_l, sk>>>(q);
+                CQ_LAUNCHED("hull_paint2_kernel", gl, smem_l);
+            } else {
+                hull_paint_kernel<WIDE><<<(unsigned)gek, kEmitWarps * 32, smem_e, sk>>>(q);
+                CQ_LAUNCHED("hull_paint_kernel", gek, smem_e);
+            }
             if (k == 0) prof_mark(3, st);
             return CHAQSDF_OK;
         }();

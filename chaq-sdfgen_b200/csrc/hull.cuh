@@ -63,6 +63,9 @@ struct HullParams {
     int nruns_e;             // emit runs per strip
     int L, c2;
     int merge_phase, merge_nphase;  // parallel merge: this launch repairs junctions k = 1 + phase + i*nphase
+    const uint8_t* lut;      // [2][lut_stride] byte for (class, clamped D2 in [0, c2]); spreads <= 256 only, else null
+    int lut_stride, lut_nbk; // bytes per class; buckets per class of the bucketed form (0: one byte per D2)
+    unsigned* work;          // work-item counter of the persistent paint kernel of this launch (zeroed by the build kernel)
 };
 
 __host__ __device__ inline size_t hull_build_smem(int pb, int nsub, bool wide) {
@@ -177,6 +180,7 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
     const int b0 = run * p.pb, b1 = b0 + p.pb < p.nblk ? b0 + p.pb : p.nblk;
     const int s0 = b0 + sub * p.sb, s1 = s0 + p.sb < b1 ? s0 + p.sb : b1;
     const bool active = cg < p.cg1;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && p.work) *p.work = 0u;  // nobody reads it before the paint kernel of this stream
     if (NSUB == 1 && !active) return;  // no barrier below in this shape
     uint32_t* gbits = reinterpret_cast<uint32_t*>(s_hull + (size_t)cgi * p.pb * 128) + lane;
     const uint8_t* recbase = p.inter + (long long)img * p.buf_rows * p.rs;

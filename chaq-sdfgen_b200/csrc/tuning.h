@@ -15,6 +15,7 @@ struct Tuning {
     long long pipe_rows = 0;   // CHAQSDF_PIPE_ROWS   band height of the host pipeline of chaqsdf_u8 (0: automatic)
     long long pipe_first = 0;  // CHAQSDF_PIPE_FIRST  height of its first and last band (0: automatic)
     int dt2d_mode = 0;         // CHAQSDF_DT2D        0 automatic, 1 "stock" (float32 recurrence), 2 "exact"
+    int paint = 0;             // CHAQSDF_PAINT       0 automatic (table kernel when it applies), 1 "level": the level-tracking kernel
     int glyph = 0;             // CHAQSDF_GLYPH       0 automatic, 1 never use the fused small-image kernel, 2 always (when it fits)
 };
 
