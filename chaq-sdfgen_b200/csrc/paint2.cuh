@@ -87,6 +87,11 @@ __device__ __noinline__ int p2_find_change(uint32_t cring_s, int cls, int from, 
     }
 }
 
+// a row distance that is not in the ring (a site more than a block away from the block being painted)
+__device__ __noinline__ int p2_g_global(const uint8_t* rec_grp, long long rs, int r, int lane) {
+    return (int)__ldg(rec_grp + (long long)r * rs + lane);
+}
+
 template <bool DIRECT>
 struct Paint2 {
     // ---- geometry of this lane's column
@@ -112,6 +117,7 @@ struct Paint2 {
     int ecls, up, nb;        // class of the current row; distance to the nearest other-class row above; next change row
     int cur_p, cur_h;        // owner so far (row, G^2); none: -1, C2
     int nxt_p, nxt_h;        // its successor if already fetched (else -1)
+    uint32_t nzw;            // bit (b & 31): the hull word of block b is not empty (blocks of the window)
     int eblk;                // the sites after nxt (after cur) are the bits of ehw in block eblk, then the blocks after
     uint32_t ehw;
 
@@ -151,7 +157,7 @@ struct Paint2 {
     __device__ __forceinline__ int height(int r) const {
         const int b = r >> 5;
         int g;
-        if (CQ_UNLIKELY((unsigned)(b - curB + 1) >= 3u)) g = (int)__ldg(rec_grp + (long long)r * rs + lane);
+        if (CQ_UNLIKELY((unsigned)(b - curB + 1) >= 3u)) g = p2_g_global(rec_grp, rs, r, lane);
         else g = (int)lds_u8(gring_s + (r & 127) * 32 + lane);
         return (g + 1) * (g + 1);
     }
@@ -198,10 +204,19 @@ struct Paint2 {
         ehw = (s & 31) == 31 ? 0u : (hword(eblk) & (0xFFFFFFFEu << (s & 31)));
     }
     // nxt := the next site of the hull if there is one in the word being scanned or in a block that starts at a row <= limit
+    __device__ __forceinline__ void note_word(int b) {
+        const uint32_t bit = 1u << (b & 31);
+        nzw = hword(b) ? (nzw | bit) : (nzw & ~bit);
+    }
     __device__ __forceinline__ void fetch_next(int limit) {
-        while (ehw == 0u) {
-            if ((eblk + 1) * 32 > limit) { nxt_p = -1; return; }
-            ++eblk;
+        if (ehw == 0u) {
+            // the next block with a site, no further than the block of row `limit`
+            const int n = (limit >> 5) - eblk;   // blocks eblk+1 .. eblk+n may be looked at
+            if (n <= 0) { nxt_p = -1; return; }
+            uint32_t m = __funnelshift_r(nzw, nzw, (eblk + 1) & 31);  // bit k: block eblk + 1 + k
+            if (n < 32) m &= (1u << n) - 1u;
+            if (m == 0u) { eblk += n; nxt_p = -1; return; }
+            eblk += __ffs(m);
             ehw = hword(eblk);
         }
         const int j = __ffs(ehw) - 1;
@@ -283,14 +298,14 @@ struct Paint2 {
 
     // one row, all lanes in step. y = the row, jb = y - Y + bias; sp walks the owner list; bit U of t / xs / as belongs
     // to this row: a new owner starts here / this column's class changes here / some column's class changes here
-    template <int U>
+    template <int U, bool FLIPS>
     __device__ __forceinline__ void row(int y, int jb, uint32_t& sp, uint32_t t, uint32_t xs, uint32_t as, int& nbd,
                                         uint32_t& tb, int& sgn, int blk_end, int lastknown) {
         sp += ((t >> U) & 1u) << 7;
         const uint32_t e = lds_u32(sp);
         const int h = (int)(e & 0x1FFFFu);
         const int d = (jb + U) - (int)(e >> 17);  // row - owner's row
-        if ((as >> U) & 1u) {            // warp-uniform: the class changes at this row in some column of the group
+        if (FLIPS && ((as >> U) & 1u)) {  // warp-uniform: the class changes at this row in some column of the group
             if ((xs >> U) & 1u) {
                 ecls ^= 1;
                 up = 1;
@@ -318,13 +333,20 @@ struct Paint2 {
         int y = r0, jb = (r0 - Y) + kP2RelBias;
 #pragma unroll 1
         for (; y + 4 <= r1; y += 4, jb += 4, t >>= 4, xs >>= 4, as >>= 4) {
-            row<0>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
-            row<1>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
-            row<2>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
-            row<3>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+            if (as & 0xFu) {   // a class change in one of the four rows, in some column: rows one after the other
+                row<0, true>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+                row<1, true>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+                row<2, true>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+                row<3, true>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+            } else {           // straight-line code: the four rows' loads overlap
+                row<0, false>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+                row<1, false>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+                row<2, false>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+                row<3, false>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+            }
         }
 #pragma unroll 1
-        for (; y < r1; ++y, ++jb, t >>= 1, xs >>= 1, as >>= 1) row<0>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
+        for (; y < r1; ++y, ++jb, t >>= 1, xs >>= 1, as >>= 1) row<0, true>(y, jb, sp, t, xs, as, nbd, tb, sgn, Y + 32, lastknown);
         nb = nbd + r1;
     }
 
@@ -355,6 +377,8 @@ struct Paint2 {
         cp_async_wait0();
         __syncwarp();
         curB = B0;
+        nzw = 0u;
+        for (int b = B0 - reach - 1; b <= B0 + reach; ++b) note_word(b);
         const uint32_t cw0 = cword(B0);
         ecls = (int)(cw0 >> (y0 & 31)) & 1;
         {
@@ -383,6 +407,7 @@ struct Paint2 {
             cp_async_wait1();                // everything but the newest group: words <= B + reach, rows <= block B + 1
             __syncwarp();
             curB = B;
+            note_word(B + reach);
             const int lastknown = (B + reach) * 32 + 31;
             if (B > B0 && is_far(nb)) {      // block B + reach has come within reach: an open-ended class run may end there
                 const uint32_t x = cword(B + reach) ^ (ecls ? 0xFFFFFFFFu : 0u);
