@@ -9,5 +9,5 @@ if the library is missing, and every compute call fails without a CUDA device.
 The directory name has a hyphen, so import it through `load_package()` in __graft_entry__.py (importlib).
 """
 from .sdfgen import (ChaqSdfError, LIB_PATH, build_library, dist_transform_2d, lib, sdf_u8, sdf_u8_multi, sdf_u8_batched_device,  # noqa: F401
-                     sdf_u8_device, sdf_fields_device, rowscan_device, envelope_device, workspace_bytes,
+                     sdf_u8_device, sdf_u8_device_static, STATIC_SCRATCH_BYTES, sdf_fields_device, rowscan_device, envelope_device, workspace_bytes,
                      launch_count, profile_enable, profile_mean_ms, reload_tuning, sdf_u8_sharded, inter_row_bytes, shard_rows, halo_plan, exchange_halos, halo_pull_list, pull_halos, pipeline_plan, col_part, rowscan_scatter_device, fields_from_inter_device, sdf_fields_a2a, SYMBOLS)

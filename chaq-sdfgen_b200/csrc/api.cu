@@ -417,7 +417,7 @@ int part_streams(PartStreams** out) {
 // banded pass 2 as build / merge / paint (hull.cuh, paint.cuh)
 template <bool WIDE>
 int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
-                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st) {
+                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st, bool one_stream = false) {
     DevInfo di;
     if (int rc = device_info(&di)) return rc;
     if (!d_ws || ws_bytes < hull_ws_bytes(n_img, w, buf_rows)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
@@ -499,7 +499,7 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     if (g_tuning.hull_parts > 0) nparts = (int)g_tuning.hull_parts;
     if (nparts > kMaxParts) nparts = kMaxParts;
     if (nparts > p.ncg / 4) nparts = p.ncg / 4 > 0 ? p.ncg / 4 : 1;
-    if (n_img != 1 || g_prof_on) nparts = 1;
+    if (n_img != 1 || g_prof_on || one_stream) nparts = 1;
     PartStreams* ps = nullptr;
     if (nparts > 1) {
         if (int rc = part_streams(&ps)) return rc;
@@ -571,10 +571,10 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
 }
 
 int launch_hull(size_t spread, const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
-                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st) {
+                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st, bool one_stream = false) {
     if (tab->hl.cap_eff > (banded_wide(spread) ? 1025 : 256)) return fail(CHAQSDF_ERR_ARG, "internal: banded path beyond its reach");
-    if (banded_wide(spread)) return launch_hull_t<true>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st);
-    return launch_hull_t<false>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st);
+    if (banded_wide(spread)) return launch_hull_t<true>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st, one_stream);
+    return launch_hull_t<false>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st, one_stream);
 }
 int launch_pass1_banded(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
                         size_t spread, uint8_t* d_inter, cudaStream_t st) {
@@ -816,3 +816,104 @@ int chaqsdf_fields_device(const uint8_t* d_img, size_t w, size_t h, size_t strid
 }
 
 }  // extern "C"
+
+// ---- no-allocation variant (no counterpart in the reference) --------
+// chaqsdf_u8_device with its workspace AND its quantisation tables in a file-scope device array, for callers that
+// must not allocate (CUDA graph capture, serving loops). Every GPU that loads the library holds the array until exit.
+namespace {
+
+constexpr size_t kStaticTabBytes = 180224;  // LevelTable @0 (4 KB), bucketed table @4096 (36 KB), byte table @40960
+static_assert(CHAQSDF_STATIC_SCRATCH_BYTES > kStaticTabBytes && kStaticTabBytes % 256 == 0, "static scratch layout");
+static __device__ __align__(256) unsigned char g_static_scratch[CHAQSDF_STATIC_SCRATCH_BYTES];
+
+struct StaticDev {
+    uint8_t* base = nullptr;      // device address of g_static_scratch on this device (cudaGetSymbolAddress)
+    bool have = false;            // tables of (spread, asym) were enqueued into the array by the last call
+    size_t spread = 0;
+    int asym = 0;
+    Tables tab;                   // pointers into the array
+    std::string lutb, lutk;       // host copies (kept alive: they are the source of asynchronous copies)
+};
+std::mutex g_static_mu;
+std::map<int, StaticDev> g_static;
+
+// the tables of get_table() for the banded path of spreads <= 256, built on the host, nothing uploaded
+void static_build_tables(size_t spread, int asymmetric, StaticDev* d) {
+    QuantTable h;
+    build_quant_table(spread, asymmetric, &h);
+    Tables& t = d->tab;
+    build_level_table(h, &t.hl);
+    t.dq = nullptr; t.dlut = nullptr;
+    t.lutb_stride = (int)align_up((size_t)t.hl.c2 + 1, 16);
+    d->lutb.assign((size_t)2 * t.lutb_stride, '\0');
+    for (int cls = 0; cls < 2; ++cls) {
+        int m = 0;
+        for (int d2 = 0; d2 <= t.hl.c2; ++d2) {
+            while (m < 255 && t.hl.thr[cls][m + 1] <= d2) ++m;
+            d->lutb[(size_t)cls * t.lutb_stride + d2] = (char)(uint8_t)(cls ? m : 255 - m);
+        }
+    }
+    const int nbk = (t.hl.c2 >> 5) + 1;
+    const int kstride = (int)align_up((size_t)nbk * 8, 16);
+    d->lutk.assign((size_t)2 * kstride, '\0');
+    bool ok = true;
+    for (int cls = 0; cls < 2 && ok; ++cls) {
+        const uint8_t* bytes = (const uint8_t*)d->lutb.data() + (size_t)cls * t.lutb_stride;
+        uint32_t* ent = (uint32_t*)(&d->lutk[(size_t)cls * kstride]);
+        for (int i = 0; i < nbk; ++i) {
+            uint32_t m = 0;
+            for (int j = 1; j < 32 && i * 32 + j <= t.hl.c2; ++j) {
+                const int dd = (int)bytes[i * 32 + j] - (int)bytes[i * 32 + j - 1];
+                if (dd == (cls ? 1 : -1)) m |= 1u << j;
+                else if (dd != 0) ok = false;
+            }
+            ent[2 * i] = m;
+            ent[2 * i + 1] = bytes[i * 32];
+        }
+    }
+    t.lutk_stride = ok ? kstride : 0; t.lutk_nbk = ok ? nbk : 0;
+    t.dl = (LevelTable*)d->base;
+    t.dlutk = ok ? d->base + 4096 : nullptr;
+    t.dlutb = d->base + 40960;
+}
+
+}  // namespace
+
+extern "C" int chaqsdf_u8_device_static(const uint8_t* d_img, size_t w, size_t h, size_t stride, size_t offset,
+                                        int test_above, size_t spread, int asymmetric, uint8_t* d_out, void* stream) {
+    if (!d_img || !d_out) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (int rc = check_dims(w, h, spread)) return rc;
+    if (stride == 0 || offset >= stride) return fail(CHAQSDF_ERR_ARG, "bad stride/offset");
+    if (spread > 256) return fail(CHAQSDF_ERR_ARG, "chaqsdf_u8_device_static: spread > 256 is not supported by the static-scratch variant");
+    const size_t inter_bytes = align_up(h * banded_rs(w, spread), 256);
+    const size_t need = inter_bytes + hull_ws_bytes(1, w, h);
+    if (need > CHAQSDF_STATIC_SCRATCH_BYTES - kStaticTabBytes)
+        return fail(CHAQSDF_ERR_WORKSPACE, "chaqsdf_u8_device_static: image needs " + std::to_string(need) + " bytes of scratch, the static array holds " +
+                                               std::to_string(CHAQSDF_STATIC_SCRATCH_BYTES - kStaticTabBytes) + " (use chaqsdf_u8_device with a caller workspace)");
+    int dev = 0;
+    CQ_CUDA(cudaGetDevice(&dev));
+    cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    StaticDev& d = g_static[dev];
+    if (!d.base) {  // once per device, with that device current: the array's name is not a device address in host code
+        void* ptr = nullptr;
+        CQ_CUDA(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        if (!ptr) return fail(CHAQSDF_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        d.base = (uint8_t*)ptr;
+    }
+    if (!d.have || d.spread != spread || d.asym != (asymmetric ? 1 : 0)) {
+        d.have = false;
+        static_build_tables(spread, asymmetric, &d);
+        if (d.tab.hl.cap_eff > 256) return fail(CHAQSDF_ERR_ARG, "internal: banded path beyond its reach");
+        CQ_CUDA(cudaMemcpyAsync(d.tab.dl, &d.tab.hl, sizeof(LevelTable), cudaMemcpyHostToDevice, st));
+        CQ_CUDA(cudaMemcpyAsync(d.tab.dlutb, d.lutb.data(), d.lutb.size(), cudaMemcpyHostToDevice, st));
+        if (d.tab.dlutk) CQ_CUDA(cudaMemcpyAsync(d.tab.dlutk, d.lutk.data(), d.lutk.size(), cudaMemcpyHostToDevice, st));
+        d.have = true; d.spread = spread; d.asym = asymmetric ? 1 : 0;
+    }
+    uint8_t* ws = d.base + kStaticTabBytes;
+    // nothing in the workspace has to start at zero: pass 1 writes every record, the build kernel writes every hull /
+    // class word and flag and clears the paint kernel's work counter before the paint kernel of the same stream reads it
+    if (int rc = launch_pass1_banded(d_img, w, h, stride, offset, test_above, spread, ws, st)) return rc;
+    return launch_hull(spread, ws, w, h, 0, h, 1, &d.tab, d_out, ws + inter_bytes, CHAQSDF_STATIC_SCRATCH_BYTES - kStaticTabBytes - inter_bytes, st,
+                       /*one_stream=*/true);
+}

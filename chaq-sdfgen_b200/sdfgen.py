@@ -29,6 +29,7 @@ SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count
            "chaqsdf_profile_enable",
            "chaqsdf_profile_mean_ms", "dist_transform_2d",
            "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_u8_multi", "chaqsdf_pipeline_plan", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
+           "chaqsdf_u8_device_static",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
            "chaqsdf_inter_row_bytes",
            "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
@@ -68,6 +69,7 @@ def lib():
     L.chaqsdf_fields_workspace_bytes.argtypes = [sz, sz]
     L.chaqsdf_fields_workspace_bytes.restype = sz
     L.chaqsdf_u8_device.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp, sz, vp]
+    L.chaqsdf_u8_device_static.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp]
     L.chaqsdf_u8_batched_device.argtypes = [vp, sz, sz, sz, sz, sz, i, sz, i, vp, vp, sz, vp]
     L.chaqsdf_rowscan_device.argtypes = [vp, sz, sz, sz, sz, i, sz, vp, vp]
     L.chaqsdf_envelope_device.argtypes = [vp, sz, sz, sz, sz, sz, i, vp, vp, sz, vp]
@@ -182,6 +184,17 @@ def sdf_u8_device(d_img, w, h, stride=1, offset=0, test_above=True, spread=64, a
         workspace = _workspace(workspace_bytes(w, h, spread), d_img.device)
     _check(lib().chaqsdf_u8_device(_ptr(d_img), w, h, stride, offset, int(test_above), spread, int(asymmetric),
                                    _ptr(out), _ptr(workspace), workspace.numel(), _stream_ptr(stream)))
+    return out
+
+
+STATIC_SCRATCH_BYTES = 8388608  # CHAQSDF_STATIC_SCRATCH_BYTES of include/chaqsdf.h
+
+
+def sdf_u8_device_static(d_img, w, h, out, stride=1, offset=0, test_above=True, spread=64, asymmetric=False, stream=None):
+    """chaqsdf_u8_device_static: workspace and tables in the library's static device array; allocates nothing
+    (the caller passes `out`). Calls that overlap on the GPU share that array and race."""
+    _check(lib().chaqsdf_u8_device_static(_ptr(d_img), w, h, stride, offset, int(test_above), spread, int(asymmetric),
+                                          _ptr(out), _stream_ptr(stream)))
     return out
 
 

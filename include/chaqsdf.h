@@ -95,6 +95,23 @@ int chaqsdf_u8_device(const uint8_t* d_img, size_t w, size_t h, size_t stride, s
                       size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace, size_t workspace_bytes,
                       void* stream);
 
+/* ---- no-allocation variant ---------------------------------------------------------------------------
+ * No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same computation and
+ * bytes as chaqsdf_u8_device, but the workspace AND the quantisation tables live in one file-scope
+ * `static __device__` array of CHAQSDF_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library
+ * holds it until exit). The call allocates nothing on the device (no cudaMalloc / cudaFree, no streams or events):
+ * it enqueues, on `stream`, an upload of the tables when (spread, asymmetric) differ from the previous call's on
+ * this device, then the kernels. Limits: spread <= 256, and
+ *   chaqsdf_workspace_bytes(w, h, spread) <= CHAQSDF_STATIC_SCRATCH_BYTES - 180224   (e.g. 2048 x 2048 at spread 256);
+ * larger requests fail with CHAQSDF_ERR_WORKSPACE and an error string naming both numbers. All calls on a device
+ * share the array, which keeps the previous call's contents (the kernels overwrite what they read; nothing needs
+ * zeroing by the caller): calls that overlap on the GPU -- different streams without an ordering between them --
+ * race; calls on one stream, or ordered by events, are safe. */
+#define CHAQSDF_STATIC_SCRATCH_BYTES 8388608
+int chaqsdf_u8_device_static(const uint8_t* d_img, size_t w, size_t h, size_t stride, size_t offset, int test_above,
+                             size_t spread, int asymmetric, uint8_t* d_out, void* stream);
+
 /* n images of w*h pixels each, image k at d_imgs + k*w*h*stride, output k at d_out + k*w*h. Images are
  * independent (the batch is treated as separate lines, never as one tall image). */
 size_t chaqsdf_batched_workspace_bytes(size_t n, size_t w, size_t h, size_t spread);
