@@ -143,7 +143,12 @@ struct HullBuild {
                         const int g1 = (int)c.g_push(j + 1);
                         hn = g1 < L ? (g1 + 1) * (g1 + 1) : big;
                     }
-                    if (hc < big && !(2 * hc >= hp + hn + 2)) push(blk * 32 + j, hc);
+                    // Likewise a site that is never the minimum between the newest site and its successor row (both input
+                    // points) is not a vertex: after a step up in G the next ~sqrt(2G) rows are of this kind, and each of
+                    // them would be pushed and then popped by the row after it.
+                    if (hc < big && !(2 * hc >= hp + hn + 2) &&
+                        !(top_p >= 0 && hn < big && cq_dominated<WIDE>(top_p, top_h, blk * 32 + j, hc, blk * 32 + j + 1, hn)))
+                        push(blk * 32 + j, hc);
                     hp = hc; hc = hn;
                 }
             }
