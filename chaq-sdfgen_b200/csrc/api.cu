@@ -471,8 +471,8 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     const long long strips_e = (long long)n_img * p.nstrips_e;
     long long eb = (strips_e * nbo + target_e - 1) / target_e;
     eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
-    if (use_lut) {  // persistent kernel, one item per (column group, run): ~6 items per resident warp
-        eb = ((long long)n_img * p.ncg * nbo) / ((long long)di.sms * kP2Warps * 6);
+    if (use_lut) {  // persistent kernel, one item per (column group, run): ~10 items per resident warp (measured: 8-12 blocks per run at 16384^2)
+        eb = ((long long)n_img * p.ncg * nbo) / ((long long)di.sms * kP2Warps * 10);
         eb = eb < 4 ? 4 : (eb > 32 ? 32 : eb);
     }
     if (g_tuning.hull_eb > 0) eb = g_tuning.hull_eb;
@@ -496,6 +496,9 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     // are filled with other parts' work. One part when the grid is small, when profiling per kernel, or when asked.
     int nparts = 1;
     if (n_img == 1 && !g_prof_on && p.nblk >= 4) nparts = p.ncg >= 256 ? 8 : (p.ncg >= 64 ? 4 : 1);
+    // the persistent paint kernel fills the machine by itself: two parts are enough to overlap one part's junction rounds
+    // with the other's build (measured at 16384^2: 1 part 1.19 ms, 2 parts 1.18, 4 parts 1.19, 8 parts 1.29)
+    if (use_lut && nparts > 1) nparts = p.ncg >= 256 ? 2 : 1;
     if (g_tuning.hull_parts > 0) nparts = (int)g_tuning.hull_parts;
     if (nparts > kMaxParts) nparts = kMaxParts;
     if (nparts > p.ncg / 4) nparts = p.ncg / 4 > 0 ? p.ncg / 4 : 1;
