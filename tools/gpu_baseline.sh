@@ -10,8 +10,9 @@ timeout 600 python bench.py --steps 20 --warmup 3 2>/dev/null | tail -1 > gpurun
 CHAQ_BENCH_SKIP_OTHER=1 python bench.py --steps 2 --warmup 3 > gpurun_out/plain_bench.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
     env CHAQ_BENCH_SKIP_OTHER=1 python bench.py --steps 2 --warmup 3 > gpurun_out/ncu_launches.log 2>&1
-python tools/ab_pass2.py 16384 256 2 > gpurun_out/plain.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:"hull_|rowscan8" -s 8 -c 5 -f -o gpurun_out/step \
+# whole-image kernels for the per-kernel capture: one column part (in production two parts share the SMs)
+CHAQSDF_HULL_PARTS=1 python tools/ab_pass2.py 16384 256 2 > gpurun_out/plain.log 2>&1 && \
+CHAQSDF_HULL_PARTS=1 ncu --set full --clock-control none --import-source on -k regex:"hull_|rowscan8" -s 10 -c 5 -f -o gpurun_out/step \
     python tools/ab_pass2.py 16384 256 2 > gpurun_out/ncu_full.log 2>&1
 python tools/time_configs.py c2 c3 c5 > gpurun_out/configs.jsonl 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:"glyph" -s 2 -c 1 -f -o gpurun_out/glyph \
