@@ -25,6 +25,7 @@ sys.path.insert(0, ROOT)
 
 SIDE = int(os.environ.get("CHAQ_BENCH_SIDE", 16384))
 SPREAD = int(os.environ.get("CHAQ_BENCH_SPREAD", 256))
+SHARD = os.environ.get("CHAQ_BENCH_SHARD", "tband")  # N > 1: "tband" (transposed bands) or "halo" (intermediate halo)
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the pass-2 kernels, from the committed ncu --set full
 # capture named in TRAFFIC_SOURCE (regenerated whenever a pass-2 kernel changes). Only valid at the default side and
 # spread; omitted (null) otherwise.
@@ -333,8 +334,25 @@ def run_ours(args, rank, world, local_rank):
                 ev[2].record()
             return out
     else:
-        def step(ev=None):
-            return pkg.sdf_u8_sharded(d_band, w, h, SPREAD, False, rank, world, None, state, events=ev)
+        # N > 1: row bands. Default "tband": every rank pulls `spread` rows of the INPUT from its neighbours and runs the
+        # two passes on its band's transpose (pass 2 whole inside the band). "halo": pass 1 on the band, `spread` rows of
+        # the intermediate from the neighbours, pass 2 on band + halo. The variant not timed as the step is timed
+        # afterwards for the record (other_sharding in the line).
+        state_t, state_h = {}, {}
+        pkg.tband_setup(state_t, w, h, SPREAD, rank, world, None, dev)
+        for slot in (0, 1):
+            pkg.tband_input_view(state_t, rank, slot).copy_(d_band)
+        state_t["resident"] = True  # the band lives in the symmetric input buffer; the timed step copies nothing in
+        torch.cuda.synchronize()
+
+        def step_tband(ev=None):
+            return pkg.sdf_u8_sharded_t(None, w, h, SPREAD, False, rank, world, None, state_t, events=ev)
+
+        def step_halo(ev=None):
+            return pkg.sdf_u8_sharded(d_band, w, h, SPREAD, False, rank, world, None, state_h, events=ev)
+
+        step, step_other = (step_tband, step_halo) if SHARD == "tband" else (step_halo, step_tband)
+        state = state_t if SHARD == "tband" else state_h
 
     for _ in range(W):
         step()
@@ -371,7 +389,9 @@ def run_ours(args, rank, world, local_rank):
         t = torch.tensor([ms_total] + ph, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t[0].item())
-        phases = {"rowscan_ms": float(t[1]), "halo_exchange_ms": float(t[2]), "envelope_ms": float(t[3]),
+        names = ("input_halo_pull_ms", "transpose_and_scan_ms", "envelope_and_transpose_back_ms") if SHARD == "tband" else \
+                ("rowscan_ms", "halo_exchange_ms", "envelope_ms")
+        phases = {names[0]: float(t[1]), names[1]: float(t[2]), names[2]: float(t[3]),
                   "rank0_pass2_kernels_ms": None,
                   "halo": state.get("halo"), "note": "per-phase CUDA-event means, max over ranks; halo 'peer' = pairwise "
                   "device-side signals + copies out of the neighbours' peer-mapped buffers over NVLink, 'p2p' = NCCL send/recv"}
@@ -379,6 +399,7 @@ def run_ours(args, rank, world, local_rank):
     value = h * w / (ms_step * 1e-3) / 1e6
     parity_vs_n1 = None
     sharded_kernel_ms = None
+    other_sharding = None
     if dist is not None:
         # outside the timed region: every rank also runs the WHOLE image alone and compares its band, byte for byte
         whole = torch.from_numpy(img).to(dev)
@@ -388,6 +409,22 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         parity_vs_n1 = bool(flag.item())
         del whole, ref_out
+        # the other sharding variant, for the record: same timing discipline, fewer steps, checked the same way
+        for _ in range(3):
+            step_other()
+        barrier()
+        o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        o0.record()
+        for _ in range(max(3, K // 2)):
+            res_o = step_other()
+        o1.record()
+        barrier()
+        t = torch.tensor([o0.elapsed_time(o1) / max(3, K // 2), 1.0 if torch.equal(res_o, res) else 0.0], device=dev)
+        tmin = t.clone()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        other_sharding = {"variant": "halo" if SHARD == "tband" else "tband", "ms_per_step": float(t[0]),
+                          "value": h * w / (float(t[0]) * 1e-3) / 1e6, "same_bytes_as_step": bool(tmin[1].item() > 0.5)}
         # per-kernel times of one rank's pass 2 (library CUDA events), a few extra steps
         if rank == 0:
             pkg.profile_enable(True)
@@ -407,8 +444,12 @@ def run_ours(args, rank, world, local_rank):
             pkg.sdf_u8(band_host, w, h, spread=SPREAD, out=out_host)
     else:
         def e2e_step():
-            d = band_host.to(dev, non_blocking=True)
-            o = pkg.sdf_u8_sharded(d, w, h, SPREAD, False, rank, world, None, state)
+            if SHARD == "tband":  # upload straight into the symmetric input buffer of the coming call
+                pkg.tband_input_view(state_t, rank).copy_(band_host, non_blocking=True)
+                o = step_tband()
+            else:
+                d = band_host.to(dev, non_blocking=True)
+                o = pkg.sdf_u8_sharded(d, w, h, SPREAD, False, rank, world, None, state_h)
             out_host.copy_(o, non_blocking=True)
             torch.cuda.synchronize()
     for _ in range(2):
@@ -425,7 +466,8 @@ def run_ours(args, rank, world, local_rank):
         e2e_s = float(t.item())
     e2e = {"value": h * w / e2e_s / 1e6, "unit": "Mpix/s", "h2d_bytes_per_step": int(h * w), "d2h_bytes_per_step": int(h * w),
            "ms_per_step": e2e_s * 1e3, "steps": Ke, "api": "chaqsdf_u8 (host buffers)" if world == 1 else
-           "H2D + sdf_u8_sharded (rowscan, halo exchange, envelope) + D2H"}
+           ("H2D + sdf_u8_sharded_t (input halo pull, transpose, rowscan, envelope, transpose) + D2H" if SHARD == "tband" else
+            "H2D + sdf_u8_sharded (rowscan, halo exchange, envelope) + D2H")}
 
     if rank != 0:
         if dist is not None:
@@ -476,13 +518,15 @@ def run_ours(args, rank, world, local_rank):
     line = {"metric": "SDF Mpix/s (inside+outside)", "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sharding": f"row bands x{world}" + (", halo exchange of spread rows of the "
-                       f"1.125 B/px intermediate ({'pull over peer-mapped memory' if state.get('halo') == 'peer' else 'NCCL send/recv'})"
+            "config": {"workload": WORKLOAD, "sharding": f"row bands x{world}" + ((
+                       (", transposed bands: spread rows of the INPUT from the neighbours, pass 2 whole inside the band "
+                        if SHARD == "tband" else ", halo exchange of spread rows of the 1.125 B/px intermediate ") +
+                       f"({'pull over peer-mapped memory' if state.get('halo') == 'peer' else 'NCCL send/recv'})")
                        if world > 1 else ""),
                        "l2": "inputs larger than L2 (268 MB mask + 302 MB intermediate + 268 MB bitmap per step vs "
                              "126 MB L2)"},
             "roofline": roofline, "passes": passes, "phases": phases, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks, "parity_vs_n1": parity_vs_n1,
+            "clocks": clocks, "parity_vs_n1": parity_vs_n1, "other_sharding": other_sharding,
             "other_configs": other_configs(pkg, dev) if world == 1 and SIDE == 16384 and not os.environ.get("CHAQ_BENCH_SKIP_OTHER") else None}
     if phases is not None:
         phases["rank0_pass2_kernels_ms"] = sharded_kernel_ms

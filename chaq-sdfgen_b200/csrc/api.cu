@@ -20,6 +20,7 @@
 #include "paint.cuh"
 #include "paint2.cuh"
 #include "glyph.cuh"
+#include "transpose.cuh"
 #include "tuning.h"
 
 using namespace chaq;
@@ -417,7 +418,8 @@ int part_streams(PartStreams** out) {
 // banded pass 2 as build / merge / paint (hull.cuh, paint.cuh)
 template <bool WIDE>
 int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
-                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st, bool one_stream = false) {
+                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st, bool one_stream = false,
+                int col_begin = -1, int col_end = -1) {
     DevInfo di;
     if (int rc = device_info(&di)) return rc;
     if (!d_ws || ws_bytes < hull_ws_bytes(n_img, w, buf_rows)) return fail(CHAQSDF_ERR_WORKSPACE, "workspace too small");
@@ -439,9 +441,12 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     p.rs = (long long)banded_rs(w, WIDE ? 1024 : 256); p.cls_off = WIDE ? 2 * p.wp : p.wp;
     p.nblk = (int)((buf_rows + 31) / 32);
     p.ncg = (int)((w + 31) / 32); p.wc = p.ncg * 32;
-    p.nstrips = (p.ncg + kHullWarps - 1) / kHullWarps; p.n_img = (int)n_img;
-    p.nstrips_e = (p.ncg + kEmitWarps - 1) / kEmitWarps;
-    p.cg0 = 0; p.cg1 = p.ncg;
+    // column groups [cgb, cge) are processed: the whole width, or the groups covering columns [col_begin, col_end)
+    const int cgb = col_begin >= 0 ? col_begin / 32 : 0, cge = col_end >= 0 ? (col_end + 31) / 32 : p.ncg;
+    const int ncgr = cge - cgb;
+    p.nstrips = (ncgr + kHullWarps - 1) / kHullWarps; p.n_img = (int)n_img;
+    p.nstrips_e = (ncgr + kEmitWarps - 1) / kEmitWarps;
+    p.cg0 = cgb; p.cg1 = cge;
     p.out_begin = (int)out_begin; p.out_end = (int)out_end;
     p.L = tab->hl.cap_eff - 1; p.c2 = tab->hl.c2;
     // run lengths: enough CTAs to fill the machine a few times over, runs no longer than 512 rows (build) / 1024 (emit)
@@ -472,7 +477,7 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     long long eb = (strips_e * nbo + target_e - 1) / target_e;
     eb = eb < 2 ? 2 : (eb > 32 ? 32 : eb);
     if (use_lut) {  // persistent kernel, one item per (column group, run): ~10 items per resident warp (measured: 8-12 blocks per run at 16384^2)
-        eb = ((long long)n_img * p.ncg * nbo) / ((long long)di.sms * kP2Warps * 10);
+        eb = ((long long)n_img * ncgr * nbo) / ((long long)di.sms * kP2Warps * 10);
         eb = eb < 4 ? 4 : (eb > 32 ? 32 : eb);
     }
     if (g_tuning.hull_eb > 0) eb = g_tuning.hull_eb;
@@ -495,13 +500,13 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     // the tail of one part's build (SMs idle while the last heavy CTAs finish) and its latency-bound junction rounds
     // are filled with other parts' work. One part when the grid is small, when profiling per kernel, or when asked.
     int nparts = 1;
-    if (n_img == 1 && !g_prof_on && p.nblk >= 4) nparts = p.ncg >= 256 ? 8 : (p.ncg >= 64 ? 4 : 1);
+    if (n_img == 1 && !g_prof_on && p.nblk >= 4) nparts = ncgr >= 256 ? 8 : (ncgr >= 64 ? 4 : 1);
     // the persistent paint kernel fills the machine by itself: two parts are enough to overlap one part's junction rounds
     // with the other's build (measured at 16384^2: 1 part 1.19 ms, 2 parts 1.18, 4 parts 1.19, 8 parts 1.29)
-    if (use_lut && nparts > 1) nparts = p.ncg >= 256 ? 2 : 1;
+    if (use_lut && nparts > 1) nparts = ncgr >= 256 ? 2 : 1;
     if (g_tuning.hull_parts > 0) nparts = (int)g_tuning.hull_parts;
     if (nparts > kMaxParts) nparts = kMaxParts;
-    if (nparts > p.ncg / 4) nparts = p.ncg / 4 > 0 ? p.ncg / 4 : 1;
+    if (nparts > ncgr / 4) nparts = ncgr / 4 > 0 ? ncgr / 4 : 1;
     if (n_img != 1 || g_prof_on || one_stream) nparts = 1;
     PartStreams* ps = nullptr;
     if (nparts > 1) {
@@ -509,11 +514,11 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
         ps->mu.lock();
         CQ_CUDA_UNLOCK(cudaEventRecord(ps->fork, st), ps);
     }
-    const int per = ((p.ncg + nparts - 1) / nparts + 3) & ~3;  // parts start at multiples of 4 column groups
+    const int per = ((ncgr + nparts - 1) / nparts + 3) & ~3;  // parts are multiples of 4 column groups
     int rc_all = CHAQSDF_OK;
     for (int k = 0; k < nparts && rc_all == CHAQSDF_OK; ++k) {
         HullParams q = p;
-        q.cg0 = k * per; q.cg1 = q.cg0 + per < p.ncg ? q.cg0 + per : p.ncg;
+        q.cg0 = cgb + k * per; q.cg1 = q.cg0 + per < cge ? q.cg0 + per : cge;
         if (q.cg0 >= q.cg1) break;
         q.work = use_lut ? work0 + k : nullptr;
         cudaStream_t sk = k == 0 ? st : ps->s[k - 1];
@@ -574,10 +579,11 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
 }
 
 int launch_hull(size_t spread, const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
-                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st, bool one_stream = false) {
+                const Tables* tab, uint8_t* d_out, void* d_ws, size_t ws_bytes, cudaStream_t st, bool one_stream = false,
+                int col_begin = -1, int col_end = -1) {
     if (tab->hl.cap_eff > (banded_wide(spread) ? 1025 : 256)) return fail(CHAQSDF_ERR_ARG, "internal: banded path beyond its reach");
-    if (banded_wide(spread)) return launch_hull_t<true>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st, one_stream);
-    return launch_hull_t<false>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st, one_stream);
+    if (banded_wide(spread)) return launch_hull_t<true>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st, one_stream, col_begin, col_end);
+    return launch_hull_t<false>(d_inter, w, buf_rows, out_begin, out_end, n_img, tab, d_out, d_ws, ws_bytes, st, one_stream, col_begin, col_end);
 }
 int launch_pass1_banded(const uint8_t* d_img, size_t w, size_t rows, size_t stride, size_t offset, int test_above,
                         size_t spread, uint8_t* d_inter, cudaStream_t st) {
@@ -686,6 +692,37 @@ int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size
     p.out_begin = (int)out_begin; p.out_end = (int)out_end; p.band_rows = pl.band_rows;
     p.cap = pl.cap; p.nw = pl.nw; p.table = tab->dq; p.out = d_out; p.gring = (uint32_t*)d_workspace;
     return launch_env(pl, p, false, (cudaStream_t)stream);
+}
+
+int chaqsdf_envelope_cols_device(const void* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
+                                 size_t col_begin, size_t col_end, size_t spread, int asymmetric, uint8_t* d_out,
+                                 void* d_workspace, size_t workspace_bytes, void* stream) {
+    if (!d_inter || !d_out) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (int rc = check_dims(w, buf_rows, spread)) return rc;
+    if (out_begin >= out_end || out_end > buf_rows) return fail(CHAQSDF_ERR_ARG, "bad output row range");
+    if (col_begin >= col_end || col_end > w) return fail(CHAQSDF_ERR_ARG, "bad column range");
+    if (!banded(spread)) return fail(CHAQSDF_ERR_ARG, "column ranges need spread <= 1024");
+    const Tables* tab;
+    if (int rc = get_table(spread, asymmetric, &tab)) return rc;
+    return launch_hull(spread, (const uint8_t*)d_inter, w, buf_rows, out_begin, out_end, 1, tab, d_out, d_workspace,
+                       workspace_bytes, (cudaStream_t)stream, false, (int)col_begin, (int)col_end);
+}
+
+// dst[c * dst_pitch + r] = src[r * src_pitch + c] (transpose.cuh)
+int chaqsdf_transpose_u8_device(const uint8_t* d_src, size_t src_pitch, size_t rows, size_t cols, uint8_t* d_dst,
+                                size_t dst_pitch, void* stream) {
+    if (!d_src || !d_dst) return fail(CHAQSDF_ERR_ARG, "null pointer");
+    if (rows == 0 || cols == 0 || src_pitch < cols || dst_pitch < rows) return fail(CHAQSDF_ERR_ARG, "bad transpose shape");
+    const size_t tr = (rows + kTposeTile - 1) / kTposeTile, tc = (cols + kTposeTile - 1) / kTposeTile;
+    if (tr > 65535 || tc > 0x7fffffff) return fail(CHAQSDF_ERR_ARG, "transpose shape too large");
+    TposeParams tp;
+    tp.src = d_src; tp.dst = d_dst; tp.src_pitch = (long long)src_pitch; tp.dst_pitch = (long long)dst_pitch;
+    tp.rows = (int)rows; tp.cols = (int)cols;
+    tp.vec_in = src_pitch % 16 == 0 && reinterpret_cast<uintptr_t>(d_src) % 16 == 0;
+    tp.vec_out = dst_pitch % 16 == 0 && reinterpret_cast<uintptr_t>(d_dst) % 16 == 0;
+    transpose_u8_kernel<<<dim3((unsigned)tc, (unsigned)tr), kTposeThreads, 0, (cudaStream_t)stream>>>(tp);
+    CQ_LAUNCHED("transpose_u8_kernel", tc * tr, 0);
+    return CHAQSDF_OK;
 }
 
 int chaqsdf_u8_batched_device(const uint8_t* d_imgs, size_t n, size_t w, size_t h, size_t stride, size_t offset,
@@ -920,3 +957,9 @@ extern "C" int chaqsdf_u8_device_static(const uint8_t* d_img, size_t w, size_t h
     return launch_hull(spread, ws, w, h, 0, h, 1, &d.tab, d_out, ws + inter_bytes, CHAQSDF_STATIC_SCRATCH_BYTES - kStaticTabBytes - inter_bytes, st,
                        /*one_stream=*/true);
 }
+
+#ifdef CQ_BUILD_TRACE
+extern "C" int chaqsdf_debug_build_trace(unsigned long long* out, int n) {
+    return cudaMemcpyFromSymbol(out, g_build_trace, (size_t)n * 3 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 2;
+}
+#endif

@@ -68,15 +68,19 @@ struct HullParams {
     unsigned* work;          // work-item counter of the persistent paint kernel of this launch (zeroed by the build kernel)
 };
 
+// Staged blocks of row distances per warp (a ring, filled one block ahead by cp.async). Two: the block being pushed and
+// the next. A longer ring, so that pops find heights in shared memory, measured neutral (8 blocks: 0.52 -> 0.54 ms at
+// 16384^2): the slow warps of this kernel are bound by instruction issue, not by those loads (tools/build_trace.py).
+constexpr int kHullRing = 2;
 __host__ __device__ inline size_t hull_build_smem(int pb, int nsub, bool wide) {
-    return (size_t)kHullWarps * ((size_t)nsub * 2 * (wide ? 2048 : 1024) + (size_t)pb * 128);
+    return (size_t)kHullWarps * ((size_t)nsub * kHullRing * (wide ? 2048 : 1024) + (size_t)pb * 128);
 }
 
 template <bool WIDE>
 struct HullBuildCtx {
     typedef typename GVal<WIDE>::T G;
     static constexpr int kSlot = 1024 * (int)sizeof(G);  // one staged block: 32 rows x 32 columns
-    const uint8_t* gst;      // staging (2 blocks), generic pointer at lane 0
+    const uint8_t* gst;      // staging ring (kHullRing blocks, block b in slot b % kHullRing), generic pointer at lane 0
     uint32_t gst_s;          // the same, shared-space address
     uint32_t* bits;          // run's hull words, already offset by lane
     const uint8_t* rec0;     // record of buffer row 0 at this warp's first column
@@ -105,8 +109,9 @@ struct HullBuildCtx {
     }
     __device__ __forceinline__ void block_begin(int blk) {
         __syncwarp();
-        if (blk == blk_first) { slot = 0; issue(blk, 0); } else slot ^= 1;
-        issue(blk + 1, slot ^ 1);
+        slot = blk & (kHullRing - 1);
+        if (blk == blk_first) issue(blk, slot);
+        issue(blk + 1, (blk + 1) & (kHullRing - 1));  // takes the slot of block blk + 1 - kHullRing
         int r = blk * 32 + lane;
         r = r < nrows ? r : nrows - 1;
         craw = __ldg(reinterpret_cast<const uint32_t*>(cls0 + (long long)r * rs));
@@ -139,7 +144,12 @@ struct HullBuildCtx {
         return __all_sync(0xffffffffu, __vcmpgeu4(m, lim) == 0xFFFFFFFFu);
     }
     __device__ __forceinline__ uint32_t g_push(int j) const { return reinterpret_cast<const G*>(gst + slot * kSlot)[j * 32 + lane]; }
-    __device__ __forceinline__ uint32_t g_row(int r) const { return g_load<WIDE>(rec_lane + (unsigned)r * rs32); }
+    __device__ __forceinline__ uint32_t g_row(int r) const {
+        const int b = r >> 5;
+        if (b > cur_blk - (kHullRing - 1) && b >= blk_first)  // blocks cur_blk - (kHullRing - 2) .. cur_blk are in the ring
+            return reinterpret_cast<const G*>(gst + (b & (kHullRing - 1)) * kSlot)[(r & 31) * 32 + lane];
+        return g_load<WIDE>(rec_lane + (unsigned)r * rs32);
+    }
     __device__ __forceinline__ uint32_t bits_ld(int i) const { return bits[i * 32]; }
     __device__ __forceinline__ void bits_st(int i, uint32_t v) { bits[i * 32] = v; }
     __device__ __forceinline__ void block_end(int blk, uint32_t word) {
@@ -187,7 +197,7 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
     int lag = p.L;
     asm volatile("" : "+r"(lag));
     if (active && s0 < s1) {
-        uint8_t* stage = s_hull + (size_t)kHullWarps * p.pb * 128 + (size_t)warp * 2 * HullBuildCtx<WIDE>::kSlot;
+        uint8_t* stage = s_hull + (size_t)kHullWarps * p.pb * 128 + (size_t)warp * kHullRing * HullBuildCtx<WIDE>::kSlot;
         HullBuildCtx<WIDE> c;
         c.gst = stage; c.gst_s = smem_u32(stage);
         c.bits = gbits + (s0 - b0) * 32;
@@ -219,8 +229,24 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
     }
 }
 
+#ifdef CQ_BUILD_TRACE
+__device__ unsigned long long g_build_trace[3 * 16384];
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#endif
 template <bool WIDE>
-__global__ void __launch_bounds__(kHullWarps * 32, WIDE ? 8 : 10) hull_build_kernel(HullParams p) { hull_build_body<1, WIDE>(p); }
+__global__ void __launch_bounds__(kHullWarps * 32, WIDE ? 8 : 10) hull_build_kernel(HullParams p) {
+#ifdef CQ_BUILD_TRACE
+    unsigned long long t0 = gtimer();
+#endif
+    hull_build_body<1, WIDE>(p);
+#ifdef CQ_BUILD_TRACE
+    __syncthreads();
+    if (threadIdx.x == 0 && blockIdx.x < 16384) {
+        unsigned sm; asm volatile("mov.u32 %0, %smid;" : "=r"(sm));
+        g_build_trace[3 * blockIdx.x] = t0; g_build_trace[3 * blockIdx.x + 1] = gtimer(); g_build_trace[3 * blockIdx.x + 2] = sm;
+    }
+#endif
+}
 template <bool WIDE>
 __global__ void __launch_bounds__(kHullWarps * 32 * 4, 2) hull_build4_kernel(HullParams p) { hull_build_body<4, WIDE>(p); }
 

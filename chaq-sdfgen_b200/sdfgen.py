@@ -29,7 +29,7 @@ SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count
            "chaqsdf_profile_enable",
            "chaqsdf_profile_mean_ms", "dist_transform_2d",
            "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_u8_multi", "chaqsdf_pipeline_plan", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
-           "chaqsdf_u8_device_static",
+           "chaqsdf_u8_device_static", "chaqsdf_envelope_cols_device", "chaqsdf_transpose_u8_device",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
            "chaqsdf_inter_row_bytes",
            "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
@@ -73,6 +73,8 @@ def lib():
     L.chaqsdf_u8_batched_device.argtypes = [vp, sz, sz, sz, sz, sz, i, sz, i, vp, vp, sz, vp]
     L.chaqsdf_rowscan_device.argtypes = [vp, sz, sz, sz, sz, i, sz, vp, vp]
     L.chaqsdf_envelope_device.argtypes = [vp, sz, sz, sz, sz, sz, i, vp, vp, sz, vp]
+    L.chaqsdf_envelope_cols_device.argtypes = [vp, sz, sz, sz, sz, sz, sz, sz, i, vp, vp, sz, vp]
+    L.chaqsdf_transpose_u8_device.argtypes = [vp, sz, sz, sz, vp, sz, vp]
     L.chaqsdf_fields_device.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     L.chaqsdf_col_part.argtypes = [sz, sz, sz, C.POINTER(sz), C.POINTER(sz)]
     L.chaqsdf_col_part.restype = sz
@@ -396,6 +398,149 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
     if events:
         events[3].record()
     return out
+
+
+# ---------------------------------------------------------------- transposed row bands (SURVEY.md 8(e) "row bands throughout")
+def transpose_u8_device(src_ptr, src_pitch, rows, cols, dst_ptr, dst_pitch, stream=None):
+    """dst[c*dst_pitch + r] = src[r*src_pitch + c] on the device (raw device addresses)."""
+    _check(lib().chaqsdf_transpose_u8_device(C.c_void_p(src_ptr), src_pitch, rows, cols, C.c_void_p(dst_ptr), dst_pitch,
+                                             _stream_ptr(stream)))
+
+
+def envelope_cols_device(d_inter, w, buf_rows, out_begin, out_end, col_begin, col_end, spread, asymmetric, d_out,
+                         workspace=None, stream=None):
+    nb = int(lib().chaqsdf_envelope_workspace_bytes(w, buf_rows, spread))
+    if workspace is None and nb:
+        workspace = _workspace(nb, d_inter.device)
+    _check(lib().chaqsdf_envelope_cols_device(_ptr(d_inter), w, buf_rows, out_begin, out_end, col_begin, col_end, spread,
+                                              int(asymmetric), _ptr(d_out), _ptr(workspace),
+                                              workspace.numel() if workspace is not None else 0, _stream_ptr(stream)))
+    return d_out
+
+
+def sdf_u8_tband_device(d_ext, w, ext_rows, halo_top, rows, spread, asymmetric=False, test_above=True, bufs=None, out=None):
+    """The transposed-band computation on one device. d_ext: [ext_rows][w] input bytes = `halo_top` context rows, the
+    band's `rows` rows, then the context rows below (context = `spread` rows of the image, fewer at an image edge).
+    Transposes, runs pass 1 along the original columns (length ext_rows) and pass 2 along the original rows (length w,
+    whole inside the band) for the band's columns only, and transposes back. Returns [rows][w] bytes.
+    bufs: dict that keeps the scratch tensors between calls."""
+    import torch
+    dev = d_ext.device
+    bufs = {} if bufs is None else bufs
+    key = (w, ext_rows, spread)
+    if bufs.get("key") != key:
+        bufs.clear()
+        bufs["key"] = key
+        bufs["xt"] = torch.empty((w, ext_rows), dtype=torch.uint8, device=dev)
+        bufs["inter"] = torch.empty((w, inter_row_bytes(ext_rows, spread)), dtype=torch.uint8, device=dev)
+        bufs["out_t"] = torch.empty((w, ext_rows), dtype=torch.uint8, device=dev)
+        bufs["ws"] = _workspace(int(lib().chaqsdf_envelope_workspace_bytes(ext_rows, w, spread)), dev)
+    if out is None:
+        out = torch.empty((rows, w), dtype=torch.uint8, device=dev)
+    xt, inter, out_t = bufs["xt"], bufs["inter"], bufs["out_t"]
+    transpose_u8_device(d_ext.data_ptr(), w, ext_rows, w, xt.data_ptr(), ext_rows)
+    rowscan_device(xt, ext_rows, w, spread, inter, test_above=test_above)
+    envelope_cols_device(inter, ext_rows, w, 0, w, halo_top, halo_top + rows, spread, asymmetric, out_t, workspace=bufs["ws"])
+    transpose_u8_device(out_t.data_ptr() + halo_top, ext_rows, w, rows, out.data_ptr(), w)
+    return out
+
+
+def tband_setup(state, w, h, spread, rank, world, group, dev, exchange=None):
+    """Buffers of the transposed-band path: the INPUT bands live in symmetric (peer-mapped) allocations, two slots
+    alternating by call, laid out like the halo path's intermediates (row 0 = image row r0 - halo_top), so that a rank
+    pulls its context rows of the input straight out of its neighbours' buffers."""
+    import torch
+    key = ("tband", w, h, spread, rank, world)
+    if state.get("key") == key:
+        return state
+    state.clear()
+    state["key"] = key
+    plans = [halo_plan(h, world, r, spread) for r in range(world)]
+    r0, r1, halo_top, halo_bot, _, _ = plans[rank]
+    max_rows = max(p[2] + (p[1] - p[0]) + p[3] for p in plans)
+    mode = exchange or os.environ.get("CHAQSDF_HALO") or ("peer" if dev.type == "cuda" and world > 1 else "p2p")
+    if mode == "peer" and world > 1:
+        ok = 1
+        try:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm
+            sym = symm.empty((2, max_rows, w), dtype=torch.uint8, device=dev)
+            hdl = symm.rendezvous(sym, group if group is not None else dist.group.WORLD)
+            bufs = {peer: hdl.get_buffer(peer, (2, max_rows, w), torch.uint8) for (peer, _, _) in plans[rank][4]}
+            state.update(sym=sym, hdl=hdl, peer_bufs=bufs)
+        except Exception as e:
+            ok = 0
+            state["peer_error"] = repr(e)
+        import torch.distributed as dist
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if not bool(flag.item()):
+            mode = "p2p"
+    else:
+        mode = "p2p"
+    if mode != "peer":
+        state["sym"] = torch.empty((2, max_rows, w), dtype=torch.uint8, device=dev)
+    state.update(plans=plans, step=0, halo=mode, resident=False, bufs={},
+                 out=torch.empty((r1 - r0, w), dtype=torch.uint8, device=dev))
+    return state
+
+
+def tband_input_view(state, rank, slot=None):
+    """Where this rank's band of the input goes for the next call (or for slot `slot`): a [rows][w] view."""
+    r0, r1, halo_top, _, _, _ = state["plans"][rank]
+    s = (state["step"] & 1) if slot is None else slot
+    return state["sym"][s][halo_top:halo_top + (r1 - r0)]
+
+
+def sdf_u8_sharded_t(d_band, w, h, spread, asymmetric=False, rank=0, world=1, group=None, state=None, test_above=True,
+                     events=None, exchange=None):
+    """One image of h rows sharded by row bands over `world` ranks, transposed-band variant: every rank pulls `spread`
+    rows of the INPUT from its neighbours (peer-mapped buffers over NVLink after a pairwise device-side signal, or
+    NCCL / gloo point to point), then works alone: pass 1 runs along the original columns of band + context, pass 2
+    along the original rows, which are whole inside the band, so the expensive pass does exactly 1/world of the work
+    and waits for nobody's kernels. d_band: this rank's rows, or None when the band was written into
+    tband_input_view(state, rank) (state from tband_setup). Returns this rank's output rows."""
+    if state is None:
+        state = {}
+    dev = d_band.device if d_band is not None else state["sym"].device
+    tband_setup(state, w, h, spread, rank, world, group, dev, exchange)
+    r0, r1, halo_top, halo_bot, _, _ = state["plans"][rank]
+    rows = r1 - r0
+    ext_rows = halo_top + rows + halo_bot
+    slot = state["step"] & 1
+    state["step"] += 1
+    ext = state["sym"][slot][:ext_rows]
+    if d_band is not None and not state["resident"]:
+        ext[halo_top:halo_top + rows].copy_(d_band, non_blocking=True)
+    if events:
+        events[0].record()
+    if world > 1:
+        if state["halo"] == "peer":
+            pull_halos(state, slot, rank)
+        else:
+            exchange_halos(ext, h, world, rank, spread, group)
+    if events:
+        events[1].record()
+    import torch  # noqa: F401
+    bufs = state["bufs"]
+    # the four launches of sdf_u8_tband_device, with an event between the scan and the envelope side
+    key = (w, ext_rows, spread)
+    if bufs.get("key") != key:
+        sdf_u8_tband_device(ext, w, ext_rows, halo_top, rows, spread, asymmetric, test_above, bufs, state["out"])  # allocates
+        if events:
+            events[2].record()
+            events[3].record()
+        return state["out"]
+    xt, inter, out_t = bufs["xt"], bufs["inter"], bufs["out_t"]
+    transpose_u8_device(ext.data_ptr(), w, ext_rows, w, xt.data_ptr(), ext_rows)
+    rowscan_device(xt, ext_rows, w, spread, inter, test_above=test_above)
+    if events:
+        events[2].record()
+    envelope_cols_device(inter, ext_rows, w, 0, w, halo_top, halo_top + rows, spread, asymmetric, out_t, workspace=bufs["ws"])
+    transpose_u8_device(out_t.data_ptr() + halo_top, ext_rows, w, rows, state["out"].data_ptr(), w)
+    if events:
+        events[3].record()
+    return state["out"]
 
 
 # ---------------------------------------------------------------- exact fields over several GPUs (all-to-all, variant E1)

@@ -139,6 +139,22 @@ int chaqsdf_envelope_device(const void* d_inter, size_t w, size_t buf_rows, size
                             size_t spread, int asymmetric, uint8_t* d_out, void* d_workspace,
                             size_t workspace_bytes, void* stream);
 
+/* Pass 2 on the column groups that cover columns [col_begin, col_end) only (spread <= 1024). d_out is still a full-width
+ * [out_end-out_begin][w] buffer; only those columns (rounded outwards to multiples of 32, clipped to w) are written.
+ * Workspace as chaqsdf_envelope_workspace_bytes(w, buf_rows, spread). For the transposed row-band sharding below. */
+int chaqsdf_envelope_cols_device(const void* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end,
+                                 size_t col_begin, size_t col_end, size_t spread, int asymmetric, uint8_t* d_out,
+                                 void* d_workspace, size_t workspace_bytes, void* stream);
+/* Byte-matrix transposition on the device: dst[c*dst_pitch + r] = src[r*src_pitch + c] for r < rows, c < cols.
+ * Transposed row bands ("row bands throughout"): a rank that owns rows [r0, r1) of a big image takes
+ * those rows plus `spread` rows of the INPUT on either side, transposes them, and runs pass 1 along the original
+ * columns (the only pass that looks across the band's edges, and the cheap one) and pass 2 along the original rows,
+ * which are whole inside the band: chaqsdf_rowscan_device on the transposed bytes, chaqsdf_envelope_cols_device on
+ * the band's columns, and a transposition back. Replaces nothing in the reference (openmp/df.c:125-136 transposes
+ * between its two passes for the same reason: df.c:94). */
+int chaqsdf_transpose_u8_device(const uint8_t* d_src, size_t src_pitch, size_t rows, size_t cols, uint8_t* d_dst,
+                                size_t dst_pitch, void* stream);
+
 /* ---- exact fields, for parity ---------------------------------------------------------------------
  * Unwindowed exact EDT. Any output may be NULL. d2_in/d2_out: int32 squared distance to the nearest
  * inside/outside pixel (CHAQSDF_D2_INF if none). f_in/f_out: sqrtf of those (+INF if none) = the reference's

@@ -302,6 +302,56 @@ def test_row_band_sharding_single_process(pkg, oracle):
               assert np.array_equal(out.cpu().numpy(), want[r0:r1]), (world, rank)
 
 
+def test_transpose_u8(pkg):
+    """chaqsdf_transpose_u8_device on aligned, ragged and unaligned operands, against torch."""
+    g = torch.Generator(device="cuda").manual_seed(3)
+    for (rows, cols, off, sp_extra, dp_extra) in ((256, 128, 0, 0, 0), (64, 64, 0, 0, 0), (257, 333, 0, 0, 0), (1000, 70, 5, 3, 1),
+                                                  (33, 2049, 16, 16, 0), (1, 1, 0, 0, 0)):
+        src_pitch, dst_pitch = cols + off + sp_extra, rows + dp_extra
+        src = torch.randint(0, 256, (rows, src_pitch), dtype=torch.uint8, device="cuda", generator=g)
+        dst = torch.full((cols, dst_pitch), 0xAB, dtype=torch.uint8, device="cuda")
+        pkg.transpose_u8_device(src.data_ptr() + off, src_pitch, rows, cols, dst.data_ptr(), dst_pitch)
+        torch.cuda.synchronize()
+        assert torch.equal(dst[:, :rows], src[:, off:off + cols].t()), (rows, cols, off)
+        assert bool((dst[:, rows:] == 0xAB).all()), "wrote past the destination rows"
+
+
+def test_transposed_band_sharding_single_process(pkg, oracle):
+    """The transposed-band decomposition (sdf_u8_sharded_t), emulated on one GPU: each 'rank' gets its band plus
+    `spread` rows of the INPUT on either side, as the peer pull delivers them, and works alone; its rows must equal
+    the unsharded result. Covers bands thinner than the spread (context from several neighbours), ragged band heights
+    (column ranges that do not start at a multiple of 32) and the wide (16-bit) intermediate."""
+    for (h, w, spread) in ((700, 640, 40), (515, 333, 100), (1100, 200, 300)):
+        img = oracle.syn_discs(w, h)
+        want = oracle.sdf(img, w, h, spread=spread)
+        d_img = torch.from_numpy(img).cuda()
+        for world in (2, 3, 8, 32):
+            bufs = {}
+            for rank in range(world):
+                r0, r1, ht, hb, _, _ = pkg.halo_plan(h, world, rank, spread)
+                ext = d_img[r0 - ht:r1 + hb].contiguous()
+                out = pkg.sdf_u8_tband_device(ext, w, ext.shape[0], ht, r1 - r0, spread, bufs=bufs)
+                torch.cuda.synchronize()
+                assert np.array_equal(out.cpu().numpy(), want[r0:r1]), (h, w, spread, world, rank)
+
+
+def test_envelope_cols_writes_only_its_columns(pkg, oracle):
+    h, w, spread = 400, 700, 64
+    img = oracle.syn_discs(w, h)
+    want = oracle.sdf(img, w, h, spread=spread)
+    d_img = torch.from_numpy(img).cuda()
+    inter = torch.empty((h, pkg.inter_row_bytes(w, spread)), dtype=torch.uint8, device="cuda")
+    pkg.rowscan_device(d_img, w, h, spread, inter)
+    for (c0, c1) in ((0, 700), (64, 128), (100, 301), (650, 700), (31, 33)):
+        out = torch.full((h, w), 0x77, dtype=torch.uint8, device="cuda")
+        pkg.envelope_cols_device(inter, w, h, 0, h, c0, c1, spread, False, out)
+        torch.cuda.synchronize()
+        got = out.cpu().numpy()
+        a, b = c0 // 32 * 32, min((c1 + 31) // 32 * 32, w)
+        assert np.array_equal(got[:, a:b], want[:, a:b]), (c0, c1)
+        assert (got[:, :a] == 0x77).all() and (got[:, b:] == 0x77).all(), (c0, c1)
+
+
 @pytest.mark.parametrize("n,spread", [(4096, 64)])
 def test_config2_full_size(pkg, oracle, ref, n, spread):
     img = oracle.syn_discs(n)
