@@ -25,7 +25,7 @@ sys.path.insert(0, ROOT)
 
 SIDE = int(os.environ.get("CHAQ_BENCH_SIDE", 16384))
 SPREAD = int(os.environ.get("CHAQ_BENCH_SPREAD", 256))
-SHARD = os.environ.get("CHAQ_BENCH_SHARD", "tband")  # N > 1: "tband" (transposed bands) or "halo" (intermediate halo)
+SHARD = os.environ.get("CHAQ_BENCH_SHARD", "halo")  # N > 1: "halo" (intermediate halo; measured faster at N = 2, 4, 8) or "tband" (transposed bands)
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the pass-2 kernels, from the committed ncu --set full
 # capture named in TRAFFIC_SOURCE (regenerated whenever a pass-2 kernel changes). Only valid at the default side and
 # spread; omitted (null) otherwise.
@@ -334,7 +334,7 @@ def run_ours(args, rank, world, local_rank):
                 ev[2].record()
             return out
     else:
-        # N > 1: row bands. Default "tband": every rank pulls `spread` rows of the INPUT from its neighbours and runs the
+        # N > 1: row bands. "tband": every rank pulls `spread` rows of the INPUT from its neighbours and runs the
         # two passes on its band's transpose (pass 2 whole inside the band). "halo": pass 1 on the band, `spread` rows of
         # the intermediate from the neighbours, pass 2 on band + halo. The variant not timed as the step is timed
         # afterwards for the record (other_sharding in the line).
