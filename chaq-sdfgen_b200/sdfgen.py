@@ -30,6 +30,7 @@ SYMBOLS = ["chaqsdf_version", "chaqsdf_last_error_string", "chaqsdf_launch_count
            "chaqsdf_profile_mean_ms", "dist_transform_2d",
            "chaqsdf_dt2d_last_status", "chaqsdf_u8", "chaqsdf_u8_multi", "chaqsdf_pipeline_plan", "chaqsdf_workspace_bytes", "chaqsdf_u8_device",
            "chaqsdf_u8_device_static", "chaqsdf_envelope_cols_device", "chaqsdf_transpose_u8_device",
+           "chaqsdf_atlas_pack", "chaqsdf_glyph_boxes_device", "chaqsdf_atlas_blit_device", "chaqsdf_atlas_u8",
            "chaqsdf_batched_workspace_bytes", "chaqsdf_u8_batched_device", "chaqsdf_rowscan_device",
            "chaqsdf_inter_row_bytes",
            "chaqsdf_envelope_workspace_bytes", "chaqsdf_envelope_device", "chaqsdf_fields_workspace_bytes",
@@ -75,6 +76,10 @@ def lib():
     L.chaqsdf_envelope_device.argtypes = [vp, sz, sz, sz, sz, sz, i, vp, vp, sz, vp]
     L.chaqsdf_envelope_cols_device.argtypes = [vp, sz, sz, sz, sz, sz, sz, sz, i, vp, vp, sz, vp]
     L.chaqsdf_transpose_u8_device.argtypes = [vp, sz, sz, sz, vp, sz, vp]
+    L.chaqsdf_atlas_pack.argtypes = [sz, vp, sz, sz, vp, C.POINTER(sz)]
+    L.chaqsdf_glyph_boxes_device.argtypes = [vp, sz, sz, sz, i, sz, vp, vp]
+    L.chaqsdf_atlas_blit_device.argtypes = [vp, sz, sz, sz, vp, vp, vp, sz, vp]
+    L.chaqsdf_atlas_u8.argtypes = [vp, sz, sz, sz, i, sz, i, sz, sz, vp, sz, C.POINTER(sz), vp, vp]
     L.chaqsdf_fields_device.argtypes = [vp, sz, sz, sz, sz, i, sz, i, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     L.chaqsdf_col_part.argtypes = [sz, sz, sz, C.POINTER(sz), C.POINTER(sz)]
     L.chaqsdf_col_part.restype = sz
@@ -398,6 +403,47 @@ def sdf_u8_sharded(d_band, w, h, spread, asymmetric=False, rank=0, world=1, grou
     if events:
         events[3].record()
     return out
+
+
+# ---------------------------------------------------------------- glyph / atlas front-end
+def atlas_pack(wh, atlas_w, pad=1):
+    """Skyline bottom-left packing (chaqsdf_atlas_pack; host only). wh: [n, 2] widths and heights.
+    Returns (xy [n, 2] uint32, atlas_h)."""
+    import numpy as np
+    wh = np.ascontiguousarray(wh, np.uint32).reshape(-1, 2)
+    xy = np.zeros_like(wh)
+    ah = C.c_size_t(0)
+    _check(lib().chaqsdf_atlas_pack(len(wh), wh.ctypes.data_as(C.c_void_p), atlas_w, pad, xy.ctypes.data_as(C.c_void_p),
+                                    C.byref(ah)))
+    return xy, int(ah.value)
+
+
+def glyph_boxes_device(d_glyphs, n, w, h, test_above=True, margin=0, stream=None):
+    import torch
+    boxes = torch.empty((n, 4), dtype=torch.int32, device=d_glyphs.device)
+    _check(lib().chaqsdf_glyph_boxes_device(_ptr(d_glyphs), n, w, h, int(test_above), margin, _ptr(boxes), _stream_ptr(stream)))
+    return boxes
+
+
+def atlas_blit_device(d_sdf, n, w, h, d_boxes, d_xy, d_atlas, atlas_w, stream=None):
+    _check(lib().chaqsdf_atlas_blit_device(_ptr(d_sdf), n, w, h, _ptr(d_boxes), _ptr(d_xy), _ptr(d_atlas), atlas_w,
+                                           _stream_ptr(stream)))
+    return d_atlas
+
+
+def atlas_u8(glyphs, n, w, h, spread=16, asymmetric=False, test_above=True, atlas_w=4096, pad=1, rows_cap=None):
+    """chaqsdf_atlas_u8: n host canvases [n, h, w] -> (atlas [atlas_h, atlas_w] uint8, boxes [n, 4], xy [n, 2])."""
+    import numpy as np
+    glyphs = np.ascontiguousarray(glyphs, np.uint8)
+    cap = rows_cap if rows_cap is not None else max(1, (n * (w + pad) * (h + pad) + atlas_w - 1) // atlas_w + h + pad)
+    atlas = np.empty((cap, atlas_w), np.uint8)
+    boxes = np.empty((n, 4), np.int32)
+    xy = np.empty((n, 2), np.uint32)
+    ah = C.c_size_t(0)
+    _check(lib().chaqsdf_atlas_u8(glyphs.ctypes.data_as(C.c_void_p), n, w, h, int(test_above), spread, int(asymmetric), atlas_w, pad,
+                                  atlas.ctypes.data_as(C.c_void_p), cap, C.byref(ah), boxes.ctypes.data_as(C.c_void_p),
+                                  xy.ctypes.data_as(C.c_void_p)))
+    return atlas[:ah.value], boxes, xy
 
 
 # ---------------------------------------------------------------- transposed row bands (SURVEY.md 8(e) "row bands throughout")

@@ -155,6 +155,27 @@ int chaqsdf_envelope_cols_device(const void* d_inter, size_t w, size_t buf_rows,
 int chaqsdf_transpose_u8_device(const uint8_t* d_src, size_t src_pitch, size_t rows, size_t cols, uint8_t* d_dst,
                                 size_t dst_pitch, void* stream);
 
+/* ---- glyph / atlas front-end and packer -------------------------------------------------
+ * The caller side of a batched glyph job: rasterised glyph canvases in, a packed SDF atlas out. The reference has no
+ * counterpart (include/stb/stb_truetype.h and stb_rect_pack.h sit unused in its submodule); csrc/atlas.cu.
+ * chaqsdf_atlas_pack (host only, no device needed): skyline bottom-left packing of n rectangles wh[2i] x wh[2i+1] into
+ *   an atlas atlas_w pixels wide, `pad` empty pixels right of and below each; writes the top-left corners to
+ *   xy[2i], xy[2i+1] and the height used to *atlas_h. Empty rectangles get (0, 0). Deterministic.
+ * chaqsdf_glyph_boxes_device: d_boxes[4i..] = {x0, y0, x1, y1} (exclusive), the bounding box of glyph i's inside pixels
+ *   (threshold as sdfgen.c:57-59) grown by `margin` and clipped to the canvas; {0,0,0,0} for a canvas without ink.
+ * chaqsdf_atlas_blit_device: copies box i of the i-th w*h canvas of d_sdf to d_atlas at (xy[2i], xy[2i+1]).
+ * chaqsdf_atlas_u8: all of it from host buffers: upload, boxes (margin = spread), chaqsdf_u8_batched_device, pack,
+ *   blit into an atlas cleared to 0 (the byte of a pixel far outside every shape), download of *atlas_h rows;
+ *   fails with CHAQSDF_ERR_WORKSPACE when *atlas_h exceeds atlas_rows_cap (then *atlas_h says what is needed). */
+int chaqsdf_atlas_pack(size_t n, const uint32_t* wh, size_t atlas_w, size_t pad, uint32_t* xy, size_t* atlas_h);
+int chaqsdf_glyph_boxes_device(const uint8_t* d_glyphs, size_t n, size_t w, size_t h, int test_above, size_t margin,
+                               int32_t* d_boxes, void* stream);
+int chaqsdf_atlas_blit_device(const uint8_t* d_sdf, size_t n, size_t w, size_t h, const int32_t* d_boxes,
+                              const uint32_t* d_xy, uint8_t* d_atlas, size_t atlas_w, void* stream);
+int chaqsdf_atlas_u8(const uint8_t* glyphs, size_t n, size_t w, size_t h, int test_above, size_t spread, int asymmetric,
+                     size_t atlas_w, size_t pad, uint8_t* atlas, size_t atlas_rows_cap, size_t* atlas_h, int32_t* boxes,
+                     uint32_t* xy);
+
 /* ---- exact fields, for parity ---------------------------------------------------------------------
  * Unwindowed exact EDT. Any output may be NULL. d2_in/d2_out: int32 squared distance to the nearest
  * inside/outside pixel (CHAQSDF_D2_INF if none). f_in/f_out: sqrtf of those (+INF if none) = the reference's

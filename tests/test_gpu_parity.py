@@ -352,6 +352,38 @@ def test_envelope_cols_writes_only_its_columns(pkg, oracle):
         assert (got[:, :a] == 0x77).all() and (got[:, b:] == 0x77).all(), (c0, c1)
 
 
+def test_glyph_atlas_front_end(pkg, oracle):
+    """SURVEY.md 8(f) row 4 through the C ABI (chaqsdf_atlas_u8): SYN-GLYPH canvases in, packed atlas out. Every glyph's
+    rectangle of the atlas holds the oracle's SDF of that canvas cropped to ink box + spread; everything else is 0."""
+    n, side, spread, aw, pad = 96, 256, 16, 2048, 1
+    glyphs = oracle.syn_glyphs(n, side)
+    glyphs[5] = 0                              # a canvas without ink: no rectangle
+    glyphs[6] = 0
+    glyphs[6, 0:3, 250:256] = 255              # ink in a corner: the box is clipped to the canvas
+    atlas, boxes, xy = pkg.atlas_u8(glyphs, n, side, side, spread=spread, atlas_w=aw, pad=pad)
+    assert atlas.shape[1] == aw
+    covered = np.zeros(atlas.shape, bool)
+    for i in range(n):
+        ys, xs = np.nonzero(glyphs[i] > 127)
+        x0, y0, x1, y1 = boxes[i].tolist()
+        if len(ys) == 0:
+            assert (x0, y0, x1, y1) == (0, 0, 0, 0)
+            continue
+        assert (x0, y0, x1, y1) == (max(xs.min() - spread, 0), max(ys.min() - spread, 0),
+                                    min(xs.max() + 1 + spread, side), min(ys.max() + 1 + spread, side)), i
+        want = oracle.sdf(glyphs[i], side, side, spread=spread)[y0:y1, x0:x1]
+        ax, ay = xy[i].tolist()
+        assert np.array_equal(atlas[ay:ay + (y1 - y0), ax:ax + (x1 - x0)], want), i
+        assert not covered[ay:ay + (y1 - y0), ax:ax + (x1 - x0)].any(), "rectangles overlap"
+        covered[ay:ay + (y1 - y0), ax:ax + (x1 - x0)] = True
+    assert (atlas[~covered] == 0).all()
+    # the device pieces on their own: boxes with another margin, blit into a caller's atlas
+    d = torch.from_numpy(glyphs).cuda()
+    b0 = pkg.glyph_boxes_device(d, n, side, side, margin=0).cpu().numpy()
+    ys, xs = np.nonzero(glyphs[0] > 127)
+    assert b0[0].tolist() == [xs.min(), ys.min(), xs.max() + 1, ys.max() + 1]
+
+
 @pytest.mark.parametrize("n,spread", [(4096, 64)])
 def test_config2_full_size(pkg, oracle, ref, n, spread):
     img = oracle.syn_discs(n)

@@ -462,3 +462,33 @@ def test_cli_argument_contract(pkg):
         assert msg in r.stderr and b"usage:" in r.stdout, args
     r = _cli("-i", "/nonexistent/x.png", "-o", "/tmp/y.png")
     assert r.returncode == 255 and b"Input file could not be opened." in r.stderr and b"usage:" not in r.stdout
+
+
+def test_atlas_pack_host_only(pkg):
+    """chaqsdf_atlas_pack: rectangles inside the atlas, pairwise disjoint including their padding,
+    deterministic, reasonably dense; degenerate inputs."""
+    rng = np.random.default_rng(5)
+    for (n, aw, pad, hi) in ((500, 1024, 2, 200), (4096, 4096, 1, 120), (50, 64, 0, 64), (1, 10, 3, 10)):
+        wh = rng.integers(1, hi + 1, (n, 2)).astype(np.uint32)
+        wh[:, 0] = np.minimum(wh[:, 0], aw)
+        if n > 10:
+            wh[3] = (0, 7)      # empty rectangles are allowed
+            wh[7] = (aw, 1)     # as wide as the atlas
+        xy, ah = pkg.atlas_pack(wh, aw, pad)
+        xy2, ah2 = pkg.atlas_pack(wh, aw, pad)
+        assert ah == ah2 and np.array_equal(xy, xy2)
+        occ = np.zeros((ah + pad + 1, aw + pad + 1), np.int32)
+        area = 0
+        for (w_, h_), (x, y) in zip(wh.tolist(), xy.tolist()):
+            if w_ == 0 or h_ == 0:
+                assert (x, y) == (0, 0)
+                continue
+            assert x + w_ <= aw and y + h_ <= ah
+            occ[y:y + h_ + pad, x:x + w_ + pad] += 1   # the rectangle and its padding
+            area += w_ * h_
+        assert (occ[:, :aw] <= 1).all(), "rectangles (with padding) overlap"
+        assert ah == max(y + h_ for (w_, h_), (x, y) in zip(wh.tolist(), xy.tolist()) if w_ and h_)
+        if n >= 500:
+            assert area / (aw * ah) > 0.75, area / (aw * ah)
+    with pytest.raises(pkg.ChaqSdfError):
+        pkg.atlas_pack(np.array([[11, 1]], np.uint32), 10, 0)
