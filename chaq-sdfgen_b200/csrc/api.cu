@@ -466,7 +466,7 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     // four warps share each run and the CTA repairs its own inner junctions. Many CTAs: one warp per run is cheaper.
     long long nsub = strips * p.nruns_b <= (long long)di.sms * 16 ? 4 : 1;
     if (g_tuning.hull_sub > 0) nsub = g_tuning.hull_sub;
-    nsub = nsub >= 4 && p.nblk >= 8 ? 4 : 1;
+    nsub = nsub >= 4 && p.nblk >= 8 ? 4 : (nsub == 2 && p.nblk >= 4 ? 2 : 1);
     if (nsub == 4 && p.pb < 8 && g_tuning.hull_pb <= 0) { p.pb = 8; p.nruns_b = (p.nblk + p.pb - 1) / p.pb; }  // sub-runs of >= 2 blocks
     p.sb = (p.pb + (int)nsub - 1) / (int)nsub; p.nsub = (int)nsub;
     const int bfirst = p.out_begin >> 5, nbo = ((p.out_end - 1) >> 5) - bfirst + 1;
@@ -495,6 +495,7 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
     if (smem_b > 48 * 1024) {
         CQ_CUDA(cudaFuncSetAttribute(hull_build_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
         CQ_CUDA(cudaFuncSetAttribute(hull_build4_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+        CQ_CUDA(cudaFuncSetAttribute(hull_build2_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
     }
     // Column parts on separate streams: the chains build -> junction rounds -> paint of different parts overlap, so
     // the tail of one part's build (SMs idle while the last heavy CTAs finish) and its latency-bound junction rounds
@@ -530,6 +531,7 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
         rc_all = [&]() -> int {
             if (k == 0) prof_mark(0, st);
             if (q.nsub == 4) hull_build4_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32 * 4, smem_b, sk>>>(q);
+            else if (q.nsub == 2) hull_build2_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32 * 2, smem_b, sk>>>(q);
             else hull_build_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32, smem_b, sk>>>(q);
             CQ_LAUNCHED(q.nsub == 4 ? "hull_build4_kernel" : "hull_build_kernel", gbk, smem_b);
             if (k == 0) prof_mark(1, st);

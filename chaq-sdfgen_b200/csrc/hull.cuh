@@ -249,6 +249,8 @@ __global__ void __launch_bounds__(kHullWarps * 32, WIDE ? 8 : 10) hull_build_ker
 }
 template <bool WIDE>
 __global__ void __launch_bounds__(kHullWarps * 32 * 4, 2) hull_build4_kernel(HullParams p) { hull_build_body<4, WIDE>(p); }
+template <bool WIDE>
+__global__ void __launch_bounds__(kHullWarps * 32 * 2, 5) hull_build2_kernel(HullParams p) { hull_build_body<2, WIDE>(p); }
 
 template <bool WIDE>
 struct HullMergeCtx {

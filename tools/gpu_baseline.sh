@@ -14,7 +14,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 CHAQSDF_HULL_PARTS=1 python tools/ab_pass2.py 16384 256 2 > gpurun_out/plain.log 2>&1 && \
 CHAQSDF_HULL_PARTS=1 ncu --set full --clock-control none --import-source on -k regex:"hull_|rowscan8" -s 10 -c 5 -f -o gpurun_out/step \
     python tools/ab_pass2.py 16384 256 2 > gpurun_out/ncu_full.log 2>&1
-python tools/time_configs.py c2 c3 c5 > gpurun_out/configs.jsonl 2>&1 && \
+python tools/time_configs.py c2 c3 c3atlas c5 > gpurun_out/configs.jsonl 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:"glyph" -s 2 -c 1 -f -o gpurun_out/glyph \
     python tools/time_configs.py c3 > gpurun_out/ncu_glyph.log 2>&1
 python tools/time_bands.py 16384 256 1 2 4 8 > gpurun_out/bands.txt 2>&1

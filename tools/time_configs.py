@@ -45,6 +45,32 @@ for c in which:
         ws = torch.empty(pkg.workspace_bytes(s, s, spread, n), dtype=torch.uint8, device="cuda")
         ms = timed(lambda: pkg.sdf_u8_batched_device(d, n, s, s, spread=spread, out=out, workspace=ws))
         px = n * s * s
+    elif c == "c3atlas":  # config 3 through the atlas front-end: boxes, SDF batch, host packing, blit (device pieces timed)
+        import time
+        import numpy as np
+        n, s, spread, aw = 4096, 256, 16, 8192
+        d = torch.from_numpy(bench.syn_glyphs(n, s)).cuda()
+        out = torch.empty((n, s, s), dtype=torch.uint8, device="cuda")
+        ws = torch.empty(pkg.workspace_bytes(s, s, spread, n), dtype=torch.uint8, device="cuda")
+        boxes = pkg.glyph_boxes_device(d, n, s, s, margin=spread)
+        b = boxes.cpu().numpy()
+        t0 = time.perf_counter()
+        xy, ah = pkg.atlas_pack(np.stack([b[:, 2] - b[:, 0], b[:, 3] - b[:, 1]], 1), aw, 1)
+        pack_ms = (time.perf_counter() - t0) * 1e3
+        d_xy = torch.from_numpy(xy).cuda()
+        atlas = torch.zeros((ah, aw), dtype=torch.uint8, device="cuda")
+
+        def run():
+            pkg.glyph_boxes_device(d, n, s, s, margin=spread)
+            pkg.sdf_u8_batched_device(d, n, s, s, spread=spread, out=out, workspace=ws)
+            atlas.zero_()
+            pkg.atlas_blit_device(out, n, s, s, boxes, d_xy, atlas, aw)
+        ms = timed(run)
+        px = n * s * s
+        used = int(((b[:, 2] - b[:, 0]) * (b[:, 3] - b[:, 1])).sum())
+        print(json.dumps({"config": "c3atlas", "device_ms": round(ms, 4), "host_pack_ms": round(pack_ms, 2), "atlas": [int(ah), aw],
+                          "fill": round(used / (ah * aw), 3), "crc": f"{zlib.crc32(atlas.cpu().numpy().tobytes()):08x}"}))
+        continue
     else:
         n, spread = 32768, 1024
         d = torch.from_numpy(bench.syn_discs(n)).cuda()
