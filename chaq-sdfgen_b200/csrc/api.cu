@@ -415,6 +415,10 @@ int part_streams(PartStreams** out) {
         }                                                                                               \
     } while (0)
 
+#ifdef CQ_BUILD_TRACE
+const uint32_t* g_dbg_order = nullptr;  // experiment: an externally supplied order of the build grid
+unsigned g_dbg_order_n = 0;
+#endif
 // banded pass 2 as build / merge / paint (hull.cuh, paint.cuh)
 template <bool WIDE>
 int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_begin, size_t out_end, size_t n_img,
@@ -530,6 +534,9 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
         const long long wpart = (long long)(q.cg1 * 32 < q.w ? q.cg1 * 32 : q.w) - q.cg0 * 32;
         rc_all = [&]() -> int {
             if (k == 0) prof_mark(0, st);
+#ifdef CQ_BUILD_TRACE
+            q.order = (g_dbg_order && gbk == (long long)g_dbg_order_n && q.nsub == 1) ? g_dbg_order : nullptr;
+#endif
             if (q.nsub == 4) hull_build4_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32 * 4, smem_b, sk>>>(q);
             else if (q.nsub == 2) hull_build2_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32 * 2, smem_b, sk>>>(q);
             else hull_build_kernel<WIDE><<<(unsigned)gbk, kHullWarps * 32, smem_b, sk>>>(q);
@@ -961,6 +968,7 @@ extern "C" int chaqsdf_u8_device_static(const uint8_t* d_img, size_t w, size_t h
 }
 
 #ifdef CQ_BUILD_TRACE
+extern "C" void chaqsdf_debug_set_build_order(const uint32_t* d_order, unsigned n) { g_dbg_order = d_order; g_dbg_order_n = n; }
 extern "C" int chaqsdf_debug_build_trace(unsigned long long* out, int n) {
     return cudaMemcpyFromSymbol(out, g_build_trace, (size_t)n * 3 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 2;
 }

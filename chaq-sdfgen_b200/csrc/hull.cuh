@@ -65,6 +65,9 @@ struct HullParams {
     int merge_phase, merge_nphase;  // parallel merge: this launch repairs junctions k = 1 + phase + i*nphase
     const uint8_t* lut;      // [2][lut_stride] byte for (class, clamped D2 in [0, c2]); spreads <= 256 only, else null
     int lut_stride, lut_nbk; // bytes per class; buckets per class of the bucketed form (0: one byte per D2)
+#ifdef CQ_BUILD_TRACE
+    const uint32_t* order;   // experiment (tools/build_order_exp.py): build CTA i works on item order[i]
+#endif
     unsigned* work;          // work-item counter of the persistent paint kernel of this launch (zeroed by the build kernel)
 };
 
@@ -183,6 +186,9 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int cgi = warp & (kHullWarps - 1), sub = NSUB > 1 ? warp / kHullWarps : 0;
     long long id = blockIdx.x;
+#ifdef CQ_BUILD_TRACE
+    if (p.order) id = (long long)__ldg(p.order + blockIdx.x);
+#endif
     const int run = (int)(id % p.nruns_b); id /= p.nruns_b;
     const int strip = (int)(id % p.nstrips);
     const int img = (int)(id / p.nstrips);
@@ -243,7 +249,8 @@ __global__ void __launch_bounds__(kHullWarps * 32, WIDE ? 8 : 10) hull_build_ker
     __syncthreads();
     if (threadIdx.x == 0 && blockIdx.x < 16384) {
         unsigned sm; asm volatile("mov.u32 %0, %smid;" : "=r"(sm));
-        g_build_trace[3 * blockIdx.x] = t0; g_build_trace[3 * blockIdx.x + 1] = gtimer(); g_build_trace[3 * blockIdx.x + 2] = sm;
+        const unsigned item = p.order ? p.order[blockIdx.x] : blockIdx.x;
+        g_build_trace[3 * item] = t0; g_build_trace[3 * item + 1] = gtimer(); g_build_trace[3 * item + 2] = sm;
     }
 #endif
 }
