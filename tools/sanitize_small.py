@@ -58,6 +58,25 @@ check("dist_transform_2d", pkg.dist_transform_2d(f.copy()).view(np.uint32), o.di
 g = rng.random((40, 40)).astype(np.float32) * 50
 r = pkg.dist_transform_2d(g.copy())
 print("dt general finite:", bool(np.isfinite(r).all()), flush=True)
+# round-2 additions: transposed bands (transposition + column-range pass 2), atlas front-end, static scratch, tall runs
+img = shapes(600, 333)
+want = o.sdf(img, 333, 600, spread=40)
+d = torch.from_numpy(img).cuda()
+for rank in range(3):
+    r0, r1, ht, hb, _, _ = pkg.halo_plan(600, 3, rank, 40)
+    ext = d[r0 - ht:r1 + hb].contiguous()
+    check(f"tband rank {rank}", pkg.sdf_u8_tband_device(ext, 333, ext.shape[0], ht, r1 - r0, 40).cpu().numpy(), want[r0:r1])
+gl = np.stack([shapes(96, 96) for _ in range(6)])
+atlas, boxes, xy = pkg.atlas_u8(gl, 6, 96, 96, spread=8, atlas_w=256, pad=1)
+okb = True
+for i in range(6):
+    x0, y0, x1, y1 = boxes[i].tolist()
+    okb &= np.array_equal(atlas[xy[i][1]:xy[i][1] + y1 - y0, xy[i][0]:xy[i][0] + x1 - x0], o.sdf(gl[i], 96, 96, spread=8)[y0:y1, x0:x1])
+check("atlas", np.array([okb]), np.array([True]))
+outs = torch.empty((600, 333), dtype=torch.uint8, device="cuda")
+check("static scratch", pkg.sdf_u8_device_static(d, 333, 600, outs, spread=40).cpu().numpy(), want)
+img = shapes(2100, 96)
+check("tall u8_device 96x2100 s100", pkg.sdf_u8_device(torch.from_numpy(img).cuda(), 96, 2100, spread=100).cpu().numpy(), o.sdf(img, 96, 2100, spread=100))
 torch.cuda.synchronize()
 print("ALL OK" if ok else "FAILURES", flush=True)
 sys.exit(0 if ok else 1)
