@@ -217,7 +217,7 @@ def test_host_pipeline_band_schedule(pkg, monkeypatch):
         assert all(b % 32 == 0 for b in bands[:-1]) and all(b > 0 for b in bands), bands
         assert all(b >= spread + 32 for b in bands[:-1]), (spread, bands)
         assert bands[0] <= max(bands) and len(bands) >= 2
-        assert max(bands) * w * stride <= (48 << 20) or max(bands) <= 2 * spread + 96, "a band is ~32 MB of input"
+        assert max(bands) * w * stride <= (48 << 20) or max(bands) <= 2 * spread + 96, "a band is ~16 MB of input"
     bands = pkg.pipeline_plan(16384, 16384, 1, 256)
     assert len(bands) >= 8 and bands[0] < bands[len(bands) // 2] and bands[-1] < bands[len(bands) // 2], bands
     monkeypatch.setenv("CHAQSDF_PIPE_ROWS", "160")
