@@ -60,6 +60,7 @@ Tuning read_tuning() {
     t.hull_sub = num("CHAQSDF_HULL_SUB");
     t.hull_eb = num("CHAQSDF_HULL_EB");
     t.hull_seq = getenv("CHAQSDF_HULL_SEQ") != nullptr;
+    t.merge_plain = getenv("CHAQSDF_MERGE_PLAIN") != nullptr;
     t.hull_parts = num("CHAQSDF_HULL_PARTS");
     t.row8_wide = getenv("CHAQSDF_ROW8_WIDE") != nullptr;
     t.pipe_rows = num("CHAQSDF_PIPE_ROWS");
@@ -552,9 +553,15 @@ int launch_hull_t(const uint8_t* d_inter, size_t w, size_t buf_rows, size_t out_
                     if (nmine <= 0) continue;
                     q.merge_phase = phase;
                     const long long thr = (long long)n_img * nmine * wpart;
-                    const unsigned gm = (unsigned)((thr + 255) / 256);
-                    hull_merge_par_kernel<WIDE><<<gm, 256, 0, sk>>>(q);
-                    CQ_LAUNCHED("hull_merge_par_kernel", gm, 0);
+                    if (!WIDE && !g_tuning.merge_plain) {  // the repair's window of hull words fits the shared-memory copy
+                        const unsigned gm = (unsigned)((thr + kMergeThreads - 1) / kMergeThreads);
+                        hull_merge_win_kernel<WIDE><<<gm, kMergeThreads, 0, sk>>>(q);
+                        CQ_LAUNCHED("hull_merge_win_kernel", gm, 0);
+                    } else {
+                        const unsigned gm = (unsigned)((thr + 255) / 256);
+                        hull_merge_par_kernel<WIDE><<<gm, 256, 0, sk>>>(q);
+                        CQ_LAUNCHED("hull_merge_par_kernel", gm, 0);
+                    }
                 }
             } else if (q.nruns_b > 1) {
                 const long long cols = (long long)n_img * wpart;

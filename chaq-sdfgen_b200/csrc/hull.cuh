@@ -225,6 +225,7 @@ __device__ __forceinline__ void hull_build_body(const HullParams p) {
             m.bits = gbits; m.rec_x = recbase + (cg * 32 + lane) * kG; m.rs32 = (unsigned)p.rs; m.blk0 = b0;
             const int hi = (b1 * 32 < p.buf_rows ? b1 * 32 : p.buf_rows) - 1;
             HullMerge<HullRunMergeCtx<WIDE>, WIDE> hm(m, lag, b0 * 32, hi);
+            hm.run_rows = p.sb * 32;
             for (int j = b0 + p.sb; j < b1; j += p.sb) hm.junction(j * 32);
         }
         __syncthreads();
@@ -282,6 +283,7 @@ __global__ void __launch_bounds__(256) hull_merge_kernel(HullParams p) {
     c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x * kG;
     c.rs32 = (unsigned)p.rs; c.wc = p.wc;
     HullMerge<HullMergeCtx<WIDE>, WIDE> hm(c, p.L, p.buf_rows);
+    hm.run_rows = WIDE ? 0 : p.pb * 32;
     for (int b = p.pb; b < p.nblk; b += p.pb) hm.junction(b * 32);
 }
 
@@ -306,7 +308,71 @@ __global__ void __launch_bounds__(256) hull_merge_par_kernel(HullParams p) {
     c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x * kG;
     c.rs32 = (unsigned)p.rs; c.wc = p.wc;
     HullMerge<HullMergeCtx<WIDE>, WIDE> hm(c, p.L, p.buf_rows);
+    hm.run_rows = WIDE ? 0 : p.pb * 32;  // hull words in global memory: galloping's re-scans of long, sparse windows cost more than they save
     hm.junction(k * p.pb * 32);
+}
+
+// The same with the hull words around the junction in shared memory: the repair finds sites by scanning hull words
+// (galloping re-scans them), and from global memory every word is a dependent L2 round trip. Every thread first copies
+// the words of its column for the blocks the repair can touch (kMergeWin each way, asynchronous copies all in flight at
+// once) into a private column of shared memory, scans there, and writes changed words through to global memory.
+// Blocks beyond the window (spreads above 256) are read from global memory as before.
+constexpr int kMergeWin = 16;      // blocks each way: 2L <= 512 rows
+constexpr int kMergeThreads = 128;
+
+template <bool WIDE>
+struct HullMergeWinCtx {
+    uint32_t* hcol;
+    const uint8_t* rec_x;
+    uint32_t* win;           // this thread's words: slot i at win[i * kMergeThreads], block b0 + i
+    unsigned rs32;
+    int wc, b0;
+    __device__ __forceinline__ uint32_t h_ld(int b) const {
+        const unsigned i = (unsigned)(b - b0);
+        return i < 2u * kMergeWin ? win[i * kMergeThreads] : hcol[(long long)b * wc];
+    }
+    __device__ __forceinline__ void h_st(int b, uint32_t v) {
+        const unsigned i = (unsigned)(b - b0);
+        if (i < 2u * kMergeWin) win[i * kMergeThreads] = v;
+        hcol[(long long)b * wc] = v;
+    }
+    __device__ __forceinline__ uint32_t g_row(int r) const { return g_load<WIDE>(rec_x + (unsigned)r * rs32); }
+};
+
+template <bool WIDE>
+__global__ void __launch_bounds__(kMergeThreads) hull_merge_win_kernel(HullParams p) {
+    __shared__ uint32_t s_win[2 * kMergeWin * kMergeThreads];
+    constexpr int kG = (int)sizeof(typename GVal<WIDE>::T);
+    const long long t = (long long)blockIdx.x * kMergeThreads + threadIdx.x;
+    const int njun = p.nruns_b - 1;
+    const int nmine = (njun - p.merge_phase + p.merge_nphase - 1) / p.merge_nphase;
+    const int x0 = p.cg0 * 32, wpart = min(p.cg1 * 32, p.w) - x0;
+    const long long per_img = (long long)nmine * wpart;
+    if (t >= per_img * p.n_img) return;
+    const int img = (int)(t / per_img);
+    const long long r = t - (long long)img * per_img;
+    const int k = 1 + p.merge_phase + p.merge_nphase * (int)(r / wpart), x = x0 + (int)(r % wpart);
+    HullMergeWinCtx<WIDE> c;
+    c.hcol = p.hull + (long long)img * p.nblk * p.wc + x;
+    c.rec_x = p.inter + (long long)img * p.buf_rows * p.rs + x * kG;
+    c.rs32 = (unsigned)p.rs; c.wc = p.wc;
+    c.win = s_win + threadIdx.x;
+    const int kb = k * p.pb;
+    c.b0 = kb - kMergeWin;
+    {
+        const uint32_t dst = smem_u32(c.win);
+#pragma unroll
+        for (int i = 0; i < 2 * kMergeWin; ++i) {
+            const int b = c.b0 + i;
+            if (b >= 0 && b < p.nblk) cp_async4(dst + i * kMergeThreads * 4, c.hcol + (long long)b * p.wc);
+            else c.win[i * kMergeThreads] = 0u;
+        }
+        cp_async_commit();
+        cp_async_wait0();
+    }
+    HullMerge<HullMergeWinCtx<WIDE>, WIDE> hm(c, p.L, p.buf_rows);
+    hm.run_rows = p.pb * 32;
+    hm.junction(kb * 32);
 }
 
 }  // namespace chaq

@@ -176,6 +176,7 @@ struct HullMerge {
     Ctx& c;
     int L;
     int lo_row, hi_row;  // the repair looks at sites of rows [lo_row, hi_row] only (a whole buffer, or one build run)
+    int run_rows = 0;    // rows per build run if the hulls on either side of a junction are whole runs (0: unknown, walk site by site)
     CQ_HD HullMerge(Ctx& ctx, int lag, int rows) : c(ctx), L(lag), lo_row(0), hi_row(rows - 1) {}
     CQ_HD HullMerge(Ctx& ctx, int lag, int lo, int hi) : c(ctx), L(lag), lo_row(lo), hi_row(hi) {}
     CQ_HD int height(int r) {
@@ -210,6 +211,152 @@ struct HullMerge {
     }
     CQ_HD void clear(int r) { c.h_st(r >> 5, c.h_ld(r >> 5) & ~(1u << (r & 31))); }
 
+    static CQ_HD int popc32(uint32_t v) {
+#if defined(__CUDA_ARCH__)
+        return __popc(v);
+#else
+        return __builtin_popcount(v);
+#endif
+    }
+    // the n-th site (n >= 1) below row `from`, no lower than row lo; -1 if there are fewer
+    CQ_HD int nth_down(int from, int n, int lo) {
+        int r = from - 1;
+        if (r < lo) return -1;
+        int b = r >> 5;
+        const int bend = lo >> 5;
+        uint32_t bits = c.h_ld(b) & (0xFFFFFFFFu >> (31 - (r & 31)));
+        for (;;) {
+            if (b == bend) bits &= (0xFFFFFFFFu << (lo & 31));
+            const int cnt = popc32(bits);
+            if (cnt >= n) {
+                for (int k = 1; k < n; ++k) bits &= ~(1u << cq_highbit(bits));
+                return (b << 5) + cq_highbit(bits);
+            }
+            n -= cnt;
+            if (b == bend) return -1;
+            --b;
+            bits = c.h_ld(b);
+        }
+    }
+    // the n-th site (n >= 1) above row `from`, no higher than row hi; -1 if there are fewer
+    CQ_HD int nth_up(int from, int n, int hi) {
+        int r = from + 1;
+        if (r > hi) return -1;
+        int b = r >> 5;
+        const int bend = hi >> 5;
+        uint32_t bits = c.h_ld(b) & (0xFFFFFFFFu << (r & 31));
+        for (;;) {
+            if (b == bend) bits &= (0xFFFFFFFFu >> (31 - (hi & 31)));
+            const int cnt = popc32(bits);
+            if (cnt >= n) {
+                for (int k = 1; k < n; ++k) bits &= bits - 1u;
+                return (b << 5) + cq_lowbit(bits);
+            }
+            n -= cnt;
+            if (b == bend) return -1;
+            ++b;
+            bits = c.h_ld(b);
+        }
+    }
+    // sites of rows [from, to] are removed
+    CQ_HD void clear_rows(int from, int to) {
+        for (int b = from >> 5; b <= (to >> 5); ++b) {
+            uint32_t m = 0xFFFFFFFFu;
+            if (b == (from >> 5)) m &= 0xFFFFFFFFu << (from & 31);
+            if (b == (to >> 5)) m &= 0xFFFFFFFFu >> (31 - (to & 31));
+            const uint32_t w = c.h_ld(b);
+            if (w & m) c.h_st(b, w & ~m);
+        }
+    }
+
+    // Along one side of a junction the sites form a convex chain (proper inside the 2L window), so "site i is dominated by
+    // its chain neighbour i+1 and the fixed site d across the junction" holds for a prefix of the chain and for no site
+    // after it: the supporting lines of a convex chain, evaluated at a point beyond its end, fall monotonically along the
+    // chain. The prefix is found by galloping (i = 0, 1, 3, 7, ...) and bisection instead of site by site: a repair that
+    // removes n sites takes O(log n) dependent look-ups of row distances, and the common repairs (0..2 sites) take the same
+    // tests as the one-by-one walk. These look-ups were what the merge kernel's duration consisted of (up to ~100 in one
+    // column at 16384^2).
+    // The chain is only known to be convex inside ONE build run (the junction at the run's other end may not have been
+    // repaired yet), so galloping stays inside the run next to the junction (rows >= lo_g); if it runs out of sites
+    // there, the walk goes on site by site down to lo.
+    // Up side: s_0 = u (height uh), s_i = the i-th site below it. Returns the number of sites to remove;
+    // nu / nuh = s_k, the first that stays.
+    CQ_HD int gallop_up(int u, int uh, int d, int dh, int lo, int lo_g, int& nu, int& nuh) {
+        int k = 0, kp = u, kh = uh;        // P(i) holds for all i < k; s_k = kp
+        int step = 1;
+        int fail = -1;                     // smallest index known to fail (-1: none yet)
+        bool fail_absent = false;          // ... because the chain ran out of sites inside the run
+        while (kp >= lo_g) {
+            const int j = fail < 0 ? k + step - 1 : k + (fail - k) / 2;   // gallop, then bisect in [k, fail)
+            const int sj = j == k ? kp : nth_down(kp, j - k, lo_g);
+            const int sj1 = sj >= 0 ? nth_down(sj, 1, lo_g) : -1;
+            bool ok = false;
+            int sjh = 0, sj1h = 0;
+            if (sj1 >= 0) {
+                sjh = j == k ? kh : height(sj);
+                sj1h = height(sj1);
+                ok = cq_dominated<WIDE>(sj1, sj1h, sj, sjh, d, dh);
+            }
+            if (ok) {
+                k = j + 1; kp = sj1; kh = sj1h;
+                if (fail < 0) step *= 2;
+            } else {
+                fail = j;
+                fail_absent = sj1 < 0;
+            }
+            if (fail >= 0 && fail == k) break;
+        }
+        if (fail < 0 || fail_absent) {     // site by site from s_k on (all of it when run_rows is unknown)
+            for (;;) {
+                const int n = down(kp - 1, lo);
+                if (n < 0) break;
+                const int nh = height(n);
+                if (!cq_dominated<WIDE>(n, nh, kp, kh, d, dh)) break;
+                ++k; kp = n; kh = nh;
+            }
+        }
+        nu = kp; nuh = kh;
+        return k;
+    }
+    // Down side: t_0 = d, t_i = the i-th site above it; u fixed; galloping inside rows <= hi_g.
+    CQ_HD int gallop_down(int u, int uh, int d, int dh, int hi, int hi_g, int& nd, int& ndh) {
+        int k = 0, kp = d, kh = dh;
+        int step = 1;
+        int fail = -1;
+        bool fail_absent = false;
+        while (kp <= hi_g) {
+            const int j = fail < 0 ? k + step - 1 : k + (fail - k) / 2;
+            const int tj = j == k ? kp : nth_up(kp, j - k, hi_g);
+            const int tj1 = tj >= 0 ? nth_up(tj, 1, hi_g) : -1;
+            bool ok = false;
+            int tjh = 0, tj1h = 0;
+            if (tj1 >= 0) {
+                tjh = j == k ? kh : height(tj);
+                tj1h = height(tj1);
+                ok = cq_dominated<WIDE>(u, uh, tj, tjh, tj1, tj1h);
+            }
+            if (ok) {
+                k = j + 1; kp = tj1; kh = tj1h;
+                if (fail < 0) step *= 2;
+            } else {
+                fail = j;
+                fail_absent = tj1 < 0;
+            }
+            if (fail >= 0 && fail == k) break;
+        }
+        if (fail < 0 || fail_absent) {
+            for (;;) {
+                const int n = up(kp + 1, hi);
+                if (n < 0) break;
+                const int nh = height(n);
+                if (!cq_dominated<WIDE>(u, uh, kp, kh, n, nh)) break;
+                ++k; kp = n; kh = nh;
+            }
+        }
+        nd = kp; ndh = kh;
+        return k;
+    }
+
     // rows < J were built (and merged) as one hull, rows >= J as another: make the union proper within 2L
     CQ_HD void junction(int J) {
         const int span = 2 * L;
@@ -218,27 +365,21 @@ struct HullMerge {
         int u1 = down(J - 1, cq_max(lo_row, d1 - span));
         if (u1 < 0) return;
         int d1h = height(d1), u1h = height(u1);
-        int u2 = -2, u2h = 0, d2 = -2, d2h = 0;  // -2: look it up
         for (;;) {
             bool changed = false;
-            if (u2 == -2) {
-                u2 = down(u1 - 1, cq_max(lo_row, d1 - span));
-                if (u2 >= 0) u2h = height(u2);
-            }
-            if (u2 >= 0 && cq_dominated<WIDE>(u2, u2h, u1, u1h, d1, d1h)) {
-                clear(u1);
-                u1 = u2; u1h = u2h; u2 = -2;
-                if (d2 >= 0 && d2 - u1 > span) d2 = -1;
+            int nu, nuh;
+            const int lo = cq_max(lo_row, d1 - span);
+            // run_rows unknown: lo_g above every site, so the galloping loop is not entered
+            if (gallop_up(u1, u1h, d1, d1h, lo, run_rows > 0 ? cq_max(lo, J - run_rows) : J, nu, nuh) > 0) {
+                clear_rows(nu + 1, u1);
+                u1 = nu; u1h = nuh;
                 changed = true;
             }
-            if (d2 == -2) {
-                d2 = up(d1 + 1, cq_min(hi_row, u1 + span));
-                if (d2 >= 0) d2h = height(d2);
-            }
-            if (d2 >= 0 && cq_dominated<WIDE>(u1, u1h, d1, d1h, d2, d2h)) {
-                clear(d1);
-                d1 = d2; d1h = d2h; d2 = -2;
-                if (u2 >= 0 && d1 - u2 > span) u2 = -1;
+            int nd, ndh;
+            const int hi = cq_min(hi_row, u1 + span);
+            if (gallop_down(u1, u1h, d1, d1h, hi, run_rows > 0 ? cq_min(hi, J + run_rows - 1) : J - 1, nd, ndh) > 0) {
+                clear_rows(d1, nd - 1);
+                d1 = nd; d1h = ndh;
                 changed = true;
             }
             if (!changed || d1 - u1 > span) break;

@@ -11,6 +11,7 @@ struct Tuning {
     long long hull_eb = 0;     // CHAQSDF_HULL_EB     blocks per paint run (0: automatic)
     long long hull_parts = 0;  // CHAQSDF_HULL_PARTS  column parts of pass 2 that run on separate streams (0: automatic, 1: none)
     bool hull_seq = false;     // CHAQSDF_HULL_SEQ    sequential junction repair (one launch) instead of rounds
+    bool merge_plain = false;  // CHAQSDF_MERGE_PLAIN junction rounds without the shared-memory window of hull words
     bool row8_wide = false;    // CHAQSDF_ROW8_WIDE   never use the several-rows-per-warp pass 1 of narrow images
     long long pipe_rows = 0;   // CHAQSDF_PIPE_ROWS   band height of the host pipeline of chaqsdf_u8 (0: automatic)
     long long pipe_first = 0;  // CHAQSDF_PIPE_FIRST  height of its first and last band (0: automatic)

@@ -146,6 +146,7 @@ static int emul3_run(const uint8_t* mask, int w, int h, size_t spread, int asym,
                 c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
                 const int hi = (b1 * 32 < h ? b1 * 32 : h) - 1;
                 HullMerge<MergeCtx, WIDE> hm(c, L, b0 * 32, hi);
+                hm.run_rows = sb * 32;
                 for (int s0 = b0 + sb; s0 < b1; s0 += sb) hm.junction(s0 * 32);
                 if (c.oob) return 1500;
             }
@@ -154,6 +155,7 @@ static int emul3_run(const uint8_t* mask, int w, int h, size_t spread, int asym,
             MergeCtx c;
             c.g = g8.data() + x; c.m = mask + x; c.stride = (size_t)w; c.nrows = h; c.nblk = nblk; c.H = &H; c.Q = &Q;
             HullMerge<MergeCtx, WIDE> hm(c, L, h);
+            hm.run_rows = build_blocks * 32;
             if (merge_order == 1) {
                 const int nphase = hull_merge_phases(L, build_blocks);
                 std::vector<int> writer(nblk);
