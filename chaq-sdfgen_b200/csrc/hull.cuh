@@ -26,6 +26,9 @@ namespace chaq {
 #ifndef CQ_HULL_WARPS
 #define CQ_HULL_WARPS 2
 #endif
+#ifndef CQ_BUILD_MINB
+#define CQ_BUILD_MINB 12  // CTAs per SM the build kernel is compiled for (10: 0.533 ms, 12: 0.511, 14: 0.519, 16: 0.515 at 16384^2)
+#endif
 constexpr int kHullWarps = CQ_HULL_WARPS;  // column groups (warps) per build CTA
 
 // Row distances in pass 1's record: one byte (spread <= 256) or, WIDE, one uint16 (spread <= 1024). Same kernels.
@@ -241,7 +244,7 @@ __device__ unsigned long long g_build_trace[3 * 16384];
 __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #endif
 template <bool WIDE>
-__global__ void __launch_bounds__(kHullWarps * 32, WIDE ? 8 : 10) hull_build_kernel(HullParams p) {
+__global__ void __launch_bounds__(kHullWarps * 32, WIDE ? 8 : CQ_BUILD_MINB) hull_build_kernel(HullParams p) {
 #ifdef CQ_BUILD_TRACE
     unsigned long long t0 = gtimer();
 #endif
