@@ -46,6 +46,35 @@ struct RowScan8Params {
     int nstrips;         // 128-column strips = wp/128; busy bytes live at record offset wp + wp/8
 };
 
+// Ramp tables for words WITH class changes inside, in shared memory (2 x 4 KB per CTA). For a byte m of the change
+// mask, entry m holds eight 16-bit values, one per pixel i of the byte:
+//   left  table: i - j, j the highest set bit of m at or below i   (distance - 1 to the change on the left inside the byte)
+//   right table: j - i, j the lowest set bit of m at or above i
+// and 0xFFFF where the byte has no such bit. A pixel's ramp is then min(table, incoming + offset), which is ONE DPX
+// instruction for two pixels (VIADDMNMX.U16x2), instead of the bit-by-bit ramp's ~9 instructions per pixel.
+struct Row8Tables {
+    uint4 tl[256], tr[256];
+};
+__device__ __forceinline__ void row8_build_tables(Row8Tables* t, int tid, int nthreads) {
+    for (int m = tid; m < 256; m += nthreads) {
+        uint32_t l[8], r[8];
+        int last = -1;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if ((m >> i) & 1) last = i;
+            l[i] = last >= 0 ? (uint32_t)(i - last) : 0xFFFFu;
+        }
+        int next = -1;
+#pragma unroll
+        for (int i = 7; i >= 0; --i) {
+            if ((m >> i) & 1) next = i;
+            r[i] = next >= 0 ? (uint32_t)(next - i) : 0xFFFFu;
+        }
+        t->tl[m] = make_uint4(l[0] | (l[1] << 16), l[2] | (l[3] << 16), l[4] | (l[5] << 16), l[6] | (l[7] << 16));
+        t->tr[m] = make_uint4(r[0] | (r[1] << 16), r[2] | (r[3] << 16), r[4] | (r[5] << 16), r[6] | (r[7] << 16));
+    }
+}
+
 // One lane's 32-pixel word: the two ramps (distance to the nearest class change on the left / on the right), their
 // minimum clamped at cap, minus one, as 32 bytes in two 128-bit stores; then the class word.
 //   PL: last pixel left of the word with a class change immediately to its left (or -kFar)
@@ -54,7 +83,7 @@ struct RowScan8Params {
 //         a mixed warp run both paths). Both ramps are then straight lines, and two pixels go per DPX instruction
 //         (VIADDMNMX.S16x2: min(a + b, c) on 16-bit halves), about six times fewer instructions than the bit-by-bit ramps.
 __device__ __forceinline__ void row8_store(uint8_t* rec, uint32_t* crec, int wi, int x0, int nvalid, int PL, int PR,
-                                           uint32_t Lw, uint32_t R, uint32_t v, int cap, bool flat) {
+                                           uint32_t Lw, uint32_t R, uint32_t v, int cap, bool flat, const Row8Tables* tab) {
     uint32_t packed[8];
     if (flat) {
         // stored byte of pixel b = min(z0 + b, y31 + 31 - b, cap) - 1; both starts are clamped at cap first, so that
@@ -74,22 +103,35 @@ __device__ __forceinline__ void row8_store(uint8_t* rec, uint32_t* crec, int wi,
             packed[i] = __byte_perm(a, b, 0x6420);
         }
     } else {
-    int dl[32];
-    int z = x0 - PL + 1;
+        // all values are "distance - 1"; 16 bits per pixel, pairs (2q, 2q+1) per register
+        uint32_t lr[16];
+        uint32_t zin = (uint32_t)min(x0 - PL, 1023);                // pixel 0 of the word, no change inside so far
 #pragma unroll
-    for (int b = 0; b < 32; ++b) {
-        z = ((Lw >> b) & 1u) ? 1 : z;
-        dl[b] = z;
-        z += 1;
-    }
-    int y = PR - (x0 + 31) + 1;
+        for (int k = 0; k < 4; ++k) {
+            const uint4 e = tab->tl[(Lw >> (8 * k)) & 0xFFu];
+            const uint32_t z2 = zin * 0x00010001u;
+            lr[4 * k + 0] = __viaddmin_u16x2(z2, 0x00010000u, e.x);  // min(incoming + i, table)
+            lr[4 * k + 1] = __viaddmin_u16x2(z2, 0x00030002u, e.y);
+            lr[4 * k + 2] = __viaddmin_u16x2(z2, 0x00050004u, e.z);
+            lr[4 * k + 3] = __viaddmin_u16x2(z2, 0x00070006u, e.w);
+            zin = (lr[4 * k + 3] >> 16) + 1u;                        // pixel 0 of the next byte
+        }
+        uint32_t yin = (uint32_t)min(PR - (x0 + 31), 1023);          // pixel 31 of the word
+        const uint32_t c2 = (uint32_t)(cap - 1) * 0x00010001u;
 #pragma unroll
-    for (int b = 31; b >= 0; --b) {
-        y = ((R >> b) & 1u) ? 1 : y;
-        const int m = min(min(dl[b], y), cap) - 1;
-        if ((b & 3) == 3) packed[b >> 2] = (uint32_t)m << 24; else packed[b >> 2] |= (uint32_t)m << (8 * (b & 3));
-        y += 1;
-    }
+        for (int k = 3; k >= 0; --k) {
+            const uint4 e = tab->tr[(R >> (8 * k)) & 0xFFu];
+            const uint32_t y2 = yin * 0x00010001u;
+            const uint32_t r0 = __viaddmin_u16x2(y2, 0x00060007u, e.x);  // pixel i: incoming + (7 - i)
+            const uint32_t r1 = __viaddmin_u16x2(y2, 0x00040005u, e.y);
+            const uint32_t r2 = __viaddmin_u16x2(y2, 0x00020003u, e.z);
+            const uint32_t r3 = __viaddmin_u16x2(y2, 0x00000001u, e.w);
+            yin = (r0 & 0xFFFFu) + 1u;                                   // pixel 7 of the byte below
+            const uint32_t a0 = __vimin3_u16x2(lr[4 * k + 0], r0, c2), a1 = __vimin3_u16x2(lr[4 * k + 1], r1, c2);
+            const uint32_t a2 = __vimin3_u16x2(lr[4 * k + 2], r2, c2), a3 = __vimin3_u16x2(lr[4 * k + 3], r3, c2);
+            packed[2 * k] = __byte_perm(a0, a1, 0x6420);
+            packed[2 * k + 1] = __byte_perm(a2, a3, 0x6420);
+        }
     }
     if (nvalid < 32) {  // pixels past the end of the row: "none"
 #pragma unroll
@@ -104,6 +146,9 @@ __device__ __forceinline__ void row8_store(uint8_t* rec, uint32_t* crec, int wi,
 
 __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel(RowScan8Params p) {
     extern __shared__ uint32_t s_bits8[];
+    __shared__ Row8Tables s_tab;
+    row8_build_tables(&s_tab, threadIdx.x, kRow8Warps * 32);
+    __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long row = (long long)blockIdx.x * kRow8Warps + warp;
     if (row >= p.rows) return;  // whole warp leaves together; no block-level barrier is used below
@@ -207,7 +252,7 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel
             if (lane < 8 && strip < p.nstrips) rec[p.wp + (p.wp >> 3) + strip] = ((B >> (4 * lane)) & 0xFu) ? 1 : 0;
         }
 
-        if (nvalid > 0) row8_store(rec, crec, wi, x0, nvalid, PL, PR, Lw, R, v, cap, (BL | BR) == 0u);
+        if (nvalid > 0) row8_store(rec, crec, wi, x0, nvalid, PL, PR, Lw, R, v, cap, (BL | BR) == 0u, &s_tab);
     }
 }
 
@@ -216,6 +261,9 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_kernel
 // 32 pixels (two 128-bit loads on the fast path), so no shared memory is needed; ballots are masked to the lane's
 // row. The arithmetic per word is the wide kernel's.
 __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_narrow_kernel(RowScan8Params p, int shift_s) {
+    __shared__ Row8Tables s_tab;
+    row8_build_tables(&s_tab, threadIdx.x, kRow8Warps * 32);
+    __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int S = 1 << shift_s, rpw = 32 >> shift_s;
     const int seg = lane >> shift_s, wi = lane & (S - 1);
@@ -272,7 +320,7 @@ __global__ void __launch_bounds__(kRow8Warps * 32, CQ_ROW8_MINB) rowscan8_narrow
     if (nvalid > 0) {
         uint8_t* rec = p.inter + (size_t)row * (size_t)p.rs;
         if ((wi & 3) == 0) rec[p.wp + (p.wp >> 3) + (wi >> 2)] = (B & (0xFu << lane) & segmask) ? 1 : 0;  // 4 lanes = one strip
-        row8_store(rec, reinterpret_cast<uint32_t*>(rec + p.wp), wi, x0, nvalid, PL, PR, Lw, R, v, cap, (BLw | BRw) == 0u);
+        row8_store(rec, reinterpret_cast<uint32_t*>(rec + p.wp), wi, x0, nvalid, PL, PR, Lw, R, v, cap, (BLw | BRw) == 0u, &s_tab);
     }
 }
 
