@@ -28,7 +28,12 @@ constexpr int kFar = 1 << 20; // "no such pixel" position offset; larger than an
 
 __device__ __forceinline__ uint32_t class_nibble(uint32_t wd, bool above) {
     // 4 pixels in a 32-bit word -> 4 class bits. above: px > 127 <=> bit 7 set; else px < 127.
-    uint32_t x = above ? (wd >> 7) & 0x01010101u : (__vcmpltu4(wd, 0x7f7f7f7fu) & 0x01010101u);
+    // One formula for both tests, plain 32-bit operations (the byte-wise SIMD compare is emulated on this architecture):
+    // px >= 127 <=> bit 7 of px, or its low seven bits are all ones (adding 1 to them carries into bit 7).
+    const uint32_t add = above ? 0u : 0x01010101u;      // above: bit 7 of px itself; else: px >= 127 ...
+    const uint32_t flip = above ? 0u : 0x01010101u;     // ... inverted: px < 127
+    const uint32_t t = ((wd & 0x7f7f7f7fu) + add) | wd;
+    const uint32_t x = ((t >> 7) & 0x01010101u) ^ flip;
     return (x * 0x01020408u) >> 24;
 }
 
