@@ -140,14 +140,18 @@ struct HullBuildCtx {
             }
             return __all_sync(0xffffffffu, __vcmpgeu2(m, lim) == 0xFFFFFFFFu);
         }
-        const uint32_t lim = (uint32_t)L * 0x01010101u;
+        // byte-wise SIMD minima are emulated on sm_100a (~7 instructions); 16-bit ones are native: even and odd bytes apart
+        uint32_t me = 0x00FF00FFu, mo = 0x00FF00FFu;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {  // 8 words per row
-            const uint32_t v = wds[lane + 32 * i];
-            const bool live = (lane >> 3) + 4 * i < rows_here;
-            m = __vminu4(m, live ? v : 0xFFFFFFFFu);
+            uint32_t v = wds[lane + 32 * i];
+            if (rows_here < 32) v = (lane >> 3) + 4 * i < rows_here ? v : 0xFFFFFFFFu;
+            me = __vminu2(me, __byte_perm(v, 0u, 0x4240));  // bytes 0 and 2 as halfwords
+            mo = __vminu2(mo, __byte_perm(v, 0u, 0x4341));  // bytes 1 and 3
         }
-        return __all_sync(0xffffffffu, __vcmpgeu4(m, lim) == 0xFFFFFFFFu);
+        const uint32_t m2 = __vminu2(me, mo);
+        const uint32_t mn = min(m2 & 0xFFFFu, m2 >> 16);
+        return __all_sync(0xffffffffu, mn >= (uint32_t)L);
     }
     __device__ __forceinline__ uint32_t g_push(int j) const { return reinterpret_cast<const G*>(gst + slot * kSlot)[j * 32 + lane]; }
     __device__ __forceinline__ uint32_t g_row(int r) const {
