@@ -206,6 +206,42 @@ def other_configs(pkg, dev):
     return res
 
 
+def config3_by_image(pkg, dev, dist, rank, world, iters=10):
+    """BASELINE config 3 over the ranks of the job (batched atlases shard by image, no communication):
+    rank r takes glyphs [r*4096/N, (r+1)*4096/N) of SYN-GLYPH, one batched call per step; time = max over ranks.
+    Check: the first 32 glyphs of the shard again through the general two-pass kernels (another implementation)."""
+    import torch
+    n_all, s, spread = 4096, 256, 16
+    g0, g1 = pkg.shard_rows(n_all, world, rank)
+    n = g1 - g0
+    d = torch.from_numpy(syn_glyphs(n, s, first=g0)).to(dev)
+    out = torch.empty((n, s, s), dtype=torch.uint8, device=dev)
+    ws = torch.empty(pkg.workspace_bytes(s, s, spread, n), dtype=torch.uint8, device=dev)
+    for _ in range(3):
+        pkg.sdf_u8_batched_device(d, n, s, s, spread=spread, out=out, workspace=ws)
+    torch.cuda.synchronize()
+    dist.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        pkg.sdf_u8_batched_device(d, n, s, s, spread=spread, out=out, workspace=ws)
+    b.record()
+    torch.cuda.synchronize()
+    k = min(32, n)
+    os.environ["CHAQSDF_GLYPH"] = "never"
+    pkg.reload_tuning()
+    other = pkg.sdf_u8_batched_device(d[:k].contiguous(), k, s, s, spread=spread)
+    torch.cuda.synchronize()
+    del os.environ["CHAQSDF_GLYPH"]
+    pkg.reload_tuning()
+    t = torch.tensor([a.elapsed_time(b) / iters, 0.0 if torch.equal(other, out[:k]) else 1.0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    return {"workload": f"4096 x SYN-GLYPH 256x256, spread 16, sharded by image over {world} GPUs (no communication)",
+            "ms": ms, "Mpix/s": n_all * s * s / ms / 1e3, "glyphs_per_rank": n,
+            "same_bytes_as_two_pass_kernels": bool(float(t[1]) == 0.0)}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -405,6 +441,7 @@ def run_ours(args, rank, world, local_rank):
     parity_vs_n1 = None
     sharded_kernel_ms = None
     other_sharding = None
+    c3_sharded = None
     if dist is not None:
         # outside the timed region: every rank also runs the WHOLE image alone and compares its band, byte for byte
         whole = torch.from_numpy(img).to(dev)
@@ -440,6 +477,11 @@ def run_ours(args, rank, world, local_rank):
             sharded_kernel_ms = name_paint(pkg.profile_mean_ms())
             pkg.profile_enable(False)
         dist.barrier()
+        if SIDE == 16384 and not os.environ.get("CHAQ_BENCH_SKIP_OTHER"):
+            try:
+                c3_sharded = config3_by_image(pkg, dev, dist, rank, world)
+            except Exception as ex:  # noqa: BLE001 -- extra information only
+                c3_sharded = {"error": repr(ex)}
 
     # ---- end to end through the host-buffer C-ABI call (pinned host memory; H2D + kernels + D2H timed) ----
     Ke = max(3, min(K, 10))
@@ -532,6 +574,7 @@ def run_ours(args, rank, world, local_rank):
                              "126 MB L2)"},
             "roofline": roofline, "passes": passes, "phases": phases, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks, "parity_vs_n1": parity_vs_n1, "other_sharding": other_sharding,
+            "config3_by_image": c3_sharded,
             "other_configs": other_configs(pkg, dev) if world == 1 and SIDE == 16384 and not os.environ.get("CHAQ_BENCH_SKIP_OTHER") else None}
     if phases is not None:
         phases["rank0_pass2_kernels_ms"] = sharded_kernel_ms
