@@ -181,6 +181,23 @@ for (h, w, spread) in ((64, 5, 7), (10, 3, 4), (37, 8, 100)):
     want = torch.arange(r0 - ht, r1 + hb, dtype=torch.int16)[:, None].expand(-1, w)
     assert torch.equal(buf, want), (rank, h, spread, buf[:, 0].tolist())
     assert ht == min(spread, r0) and hb == min(spread, h - r1)
+# the transposed-band variant's host side (sdf_u8_sharded_t): the INPUT bands live in a two-slot buffer laid out like the
+# halo path's intermediates; the band goes into tband_input_view, the context rows arrive through the same exchange
+img = (torch.arange(53 * 6, dtype=torch.int32) % 251).to(torch.uint8).reshape(53, 6)
+for spread in (5, 9, 40):
+    state = {}
+    pkg.tband_setup(state, 6, 53, spread, rank, world, None, torch.device("cpu"))
+    assert state["halo"] == "p2p"                       # no peer memory on the CPU: gloo point to point
+    r0, r1, ht, hb, _, _ = state["plans"][rank]
+    for call in range(3):                               # slots alternate by call
+        slot = state["step"] & 1
+        view = pkg.tband_input_view(state, rank)
+        assert view.shape == (r1 - r0, 6) and view.data_ptr() == state["sym"][slot][ht:ht + r1 - r0].data_ptr()
+        view.copy_(img[r0:r1])
+        ext = state["sym"][slot][:ht + (r1 - r0) + hb]
+        pkg.exchange_halos(ext, 53, world, rank, spread)
+        assert torch.equal(ext, img[r0 - ht:r1 + hb]), (rank, spread, call)
+        state["step"] += 1
 dist.barrier()
 dist.destroy_process_group()
 print("ok", rank)
