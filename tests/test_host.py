@@ -397,6 +397,24 @@ def test_hull_discs_noise_and_row_ranges(emul3, oracle):
     assert np.array_equal(got[100:333], want[100:333])
 
 
+def test_hull_junction_repair_removes_long_chains(emul3, oracle):
+    """A junction whose repair removes ~200 sites on one side: above row J every row of a column is a site of height
+    (200 - x)^2 (a vertical edge 200 columns away), from row J on the edge is adjacent (height 1), which dominates them
+    all. The repair finds how far to go by galloping + bisection inside the adjacent build run and site by site beyond
+    it; run lengths of 16, 8 and 4 blocks put the end of the chain inside the run, one run further and several runs
+    further. Mirrored vertically for the other side of the junction."""
+    for J, h in ((512, 1024), (256, 700), (384, 640)):
+        mask = np.zeros((h, 230), np.uint8)
+        mask[:J, 200:] = 1
+        mask[J:, 1:] = 1
+        for m in (mask, np.ascontiguousarray(mask[::-1])):
+            img = (m * 255).astype(np.uint8)
+            want = oracle.sdf(img, 230, h, spread=256)
+            for bb in (16, 8, 4):
+                got, _ = _emul3_u8(emul3, m, 256, False, bb, 100)
+                assert np.array_equal(got, want), (J, h, bb)
+
+
 def test_hull_merge_rounds_never_share_a_hull_word(emul3, oracle):
     """Junctions repaired in the same round run concurrently on the GPU with plain loads and stores, so two of them
     must never store the same 32-row hull word. Counting rounds in rows (ceil(4L / run length)) allowed exactly that
