@@ -6,10 +6,10 @@
 // Same mathematics as paint_core.h (plan + paint, lane = column): per half block of 16 rows each lane lists the sites
 // that own its rows (one exact integer division per site), then all lanes paint the rows in step. What differs is
 // that nothing on the per-site or per-row path waits for global memory, and the per-row work is branch free:
-//   * persistent kernel: kP2Warps warps per CTA, one CTA per SM; each warp takes (column group, run of blocks) items
+//   * persistent kernel: kP2Warps (19) warps per CTA, one CTA per SM; each warp takes (column group, run of blocks) items
 //     from a counter in the workspace (zeroed by the build kernel of the same stream);
 //   * per warp, rings in shared memory filled by cp.async ahead of use: the hull words of the blocks B-reach-1 ..
-//     B+reach+1 around the block B being painted (32 slots), the transposed class words of B .. B+reach+1 (16 slots),
+//     B+reach+1 around the block B being painted (20 slots), the transposed class words of B .. B+reach+1 (12 slots),
 //     and pass 1's row distances of the blocks B-1 .. B+2 (128 rows x 32 bytes). Sites outside that ring -- few, in
 //     sparse areas -- are read from global memory;
 //   * the block flags of the window are three ballot masks in registers;
@@ -27,12 +27,28 @@
 namespace chaq {
 
 #ifndef CQ_P2_WARPS
-#define CQ_P2_WARPS 16
+#define CQ_P2_WARPS 19
 #endif
 constexpr int kP2Warps = CQ_P2_WARPS;
 constexpr int kP2Half = 16;                      // rows per plan + paint step
 constexpr int kP2ListWords = kP2Half + 1;        // owners of one half block per lane: one per row plus the one carried in
-constexpr int kP2HullOff = 0, kP2ClsOff = 4096, kP2GOff = 4096 + 2048, kP2ListOff = 4096 + 2048 + 4096;
+// Ring sizes in blocks. The hull ring must hold blocks B-reach-1 .. B+reach+1 (19 for reach 8), the class ring blocks
+// B .. B+reach+1 (10). Powers of two (32 / 16) make the slot a mask; 20 / 12 slots save 2 KB per warp, which is three
+// more warps per SM (the kernel's time falls with its warps), for a multiply-shift per slot computation.
+#ifndef CQ_P2_HSLOTS
+#define CQ_P2_HSLOTS 20
+#endif
+#ifndef CQ_P2_CSLOTS
+#define CQ_P2_CSLOTS 12
+#endif
+constexpr int kP2HSlots = CQ_P2_HSLOTS, kP2CSlots = CQ_P2_CSLOTS;
+constexpr int kP2HullOff = 0, kP2ClsOff = kP2HSlots * 128, kP2GOff = kP2ClsOff + kP2CSlots * 128, kP2ListOff = kP2GOff + 4096;
+// slot of block b in a ring of N slots; b >= -64 (blocks above the image near its top edge)
+template <int N>
+__device__ __forceinline__ uint32_t p2_slot(int b) {
+    if ((N & (N - 1)) == 0) return (uint32_t)b & (uint32_t)(N - 1);
+    return (uint32_t)(b + 64 * N) % (uint32_t)N;
+}
 constexpr int kP2WarpBytes = kP2ListOff + kP2ListWords * 128;
 constexpr int kP2RelBias = 1024;                 // list entry = (site row - block start + bias) << 17 | G^2
 constexpr int kP2SinkOff = 128;                  // bytes after the work counters: where lanes past the image's width store
@@ -72,18 +88,18 @@ __device__ __forceinline__ int p2_ceil_div(int num, int den) {
 }
 
 // first row in [from, lastknown] whose class differs from cls, or kFarRow; lastknown is the last row of a block whose
-// class word is in the ring (slot = block & 15, stride 32 words, ring already offset by lane)
+// class word is in the ring (slot p2_slot<kP2CSlots>(block), stride 32 words, ring already offset by lane)
 __device__ __noinline__ int p2_find_change(uint32_t cring_s, int cls, int from, int lastknown) {
     if (from > lastknown) return kFarRow;
     const uint32_t flip = cls ? 0xFFFFFFFFu : 0u;
     int b = from >> 5;
     const int bend = lastknown >> 5;
-    uint32_t bits = (lds_u32(cring_s + (b & 15) * 128) ^ flip) & (0xFFFFFFFFu << (from & 31));
+    uint32_t bits = (lds_u32(cring_s + p2_slot<kP2CSlots>(b) * 128) ^ flip) & (0xFFFFFFFFu << (from & 31));
     for (;;) {
         if (bits) return (b << 5) + (__ffs(bits) - 1);
         if (b == bend) return kFarRow;
         ++b;
-        bits = lds_u32(cring_s + (b & 15) * 128) ^ flip;
+        bits = lds_u32(cring_s + p2_slot<kP2CSlots>(b) * 128) ^ flip;
     }
 }
 
@@ -123,12 +139,12 @@ struct Paint2 {
 
     // ------------------------------------------------------------------------------------------------ staging
     __device__ __forceinline__ void stage_hull(int b) {
-        const uint32_t hd = hring_s + (b & 31) * 128;
+        const uint32_t hd = hring_s + p2_slot<kP2HSlots>(b) * 128;
         if (b >= 0 && b < nblk) cp_async4(hd, hcol + (long long)b * wc);
         else sts_u32(hd, 0u);
     }
     __device__ __forceinline__ void stage_cls(int b) {
-        const uint32_t cd = cring_s + (b & 15) * 128;
+        const uint32_t cd = cring_s + p2_slot<kP2CSlots>(b) * 128;
         if (b >= 0 && b < nblk) cp_async4(cd, clst + (long long)b * wc);
         // past the buffer: the class of the last row (bit 31 of the last word; the build kernel replicates it)
         else sts_u32(cd, b < 0 ? 0u : (uint32_t)((int32_t)__ldg(clst + (long long)(nblk - 1) * wc) >> 31));
@@ -152,8 +168,8 @@ struct Paint2 {
         F1 = __ballot_sync(0xffffffffu, f == 1);
         F2 = __ballot_sync(0xffffffffu, f == 2);
     }
-    __device__ __forceinline__ uint32_t hword(int b) const { return lds_u32(hring_s + (b & 31) * 128); }
-    __device__ __forceinline__ uint32_t cword(int b) const { return lds_u32(cring_s + (b & 15) * 128); }
+    __device__ __forceinline__ uint32_t hword(int b) const { return lds_u32(hring_s + p2_slot<kP2HSlots>(b) * 128); }
+    __device__ __forceinline__ uint32_t cword(int b) const { return lds_u32(cring_s + p2_slot<kP2CSlots>(b) * 128); }
     __device__ __forceinline__ int height(int r) const {
         const int b = r >> 5;
         int g;
