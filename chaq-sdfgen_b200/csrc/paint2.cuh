@@ -30,7 +30,10 @@ namespace chaq {
 #define CQ_P2_WARPS 19
 #endif
 constexpr int kP2Warps = CQ_P2_WARPS;
-constexpr int kP2Half = 16;                      // rows per plan + paint step
+#ifndef CQ_P2_HALF
+#define CQ_P2_HALF 16
+#endif
+constexpr int kP2Half = CQ_P2_HALF;                      // rows per plan + paint step
 constexpr int kP2ListWords = kP2Half + 1;        // owners of one half block per lane: one per row plus the one carried in
 // Ring sizes in blocks. The hull ring must hold blocks B-reach-1 .. B+reach+1 (19 for reach 8), the class ring blocks
 // B .. B+reach+1 (10). Powers of two (32 / 16) make the slot a mask; 20 / 12 slots save 2 KB per warp, which is three
